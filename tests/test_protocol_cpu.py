@@ -1,0 +1,121 @@
+"""Integration tier on CPU (gloo): protocol plumbing of the six variants vs a sequential PS oracle.
+
+Covers BASELINE.json config #1 (``mnist_sync`` 1 PS + 2 workers through run.sh) and the SURVEY 4
+integration rows: sync = W pushes -> true sum -> Adam -> identical params on every worker;
+async = every push applied exactly once.
+"""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+COMMON = ["--synthetic", "--synthetic-train", "240", "--synthetic-test", "60", "--batch-size", "20",
+          "--device", "cpu", "--seed", "3", "--eval-every", "2", "--lr", "0.001"]
+
+
+def run_variant(variant, P, W, extra, timeout=240):
+    env = dict(os.environ, OMP_NUM_THREADS="2", DDL_LAUNCH_TIMEOUT=str(timeout))
+    cmd = ["bash", os.path.join(ROOT, variant, "run.sh"), str(P), str(W)] + COMMON + extra
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout + 30, env=env)
+    assert r.returncode == 0, r.stdout + r.stderr
+    return r.stdout
+
+
+def oracle_sync_run(W, steps, shard_irrelevant=True, reduce="sum", keep_prob=0.5):
+    from ddl_b200.data import synthetic_mnist
+    from ddl_b200.models import oracle
+    from ddl_b200.models.spec import REFERENCE_SPEC as spec
+    d = synthetic_mnist(240, 60, 3)
+    p = oracle.init_params(spec, 3)
+    opts = [oracle.OracleOptimizer(q, "adam", 1e-3) for q in p]
+    for s in range(steps):
+        gsum = [torch.zeros_like(q) for q in p]
+        for w in range(W):
+            b, e = d.batch_slice(s, 20, w, W, False)
+            _, g, _ = oracle.loss_and_grads(p, d.x_train[b:e], d.y_train[b:e], spec, keep_prob,
+                                            None, 3, s * W + w)
+            for a, gi in zip(gsum, g):
+                a += gi
+        for q, o, g in zip(p, opts, gsum):
+            o.step(q, g / W if reduce == "mean" else g)
+    return p
+
+
+def load_vars(path):
+    blob = torch.load(path, map_location="cpu", weights_only=False)
+    return [blob["vars"]["mnist/v%d" % i] for i in range(14)], blob
+
+
+def test_config1_mnist_sync_1ps_2workers_log_format(tmp_path):
+    out = run_variant("mnist_sync", 1, 2, ["--max-steps", "3", "--ckpt-path", str(tmp_path / "c.pt")])
+    assert re.search(r"^Worker1 epoch: 0 batch: 0 accuracy: [0-9.]+$", out, re.M)
+    assert re.search(r"^Worker2 epoch: 0 batch: 2 accuracy: [0-9.]+$", out, re.M)
+    assert len(re.findall(r"^Worker[12] final accuracy: [0-9.]+$", out, re.M)) == 2
+    assert len(re.findall(r"^Time: [0-9.e-]+$", out, re.M)) == 2
+    got, _ = load_vars(tmp_path / "c.pt")
+    want = oracle_sync_run(2, 3)
+    for g, w in zip(got, want):
+        assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
+
+
+@pytest.mark.parametrize("variant,transport", [
+    ("mnist_sync_sharding", "host"), ("mnist_sync_sharding_greedy", "host"),
+    ("mnist_sync_sharding_greedy", "nccl"),
+])
+def test_sync_sharded_matches_oracle(tmp_path, variant, transport):
+    run_variant(variant, 2, 2, ["--max-steps", "3", "--transport", transport,
+                                "--ckpt-path", str(tmp_path / "c.pt")])
+    got, _ = load_vars(tmp_path / "c.pt")
+    want = oracle_sync_run(2, 3)
+    for g, w in zip(got, want):
+        assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
+
+
+def test_collective_flat_mean_and_adam_state(tmp_path):
+    run_variant("mnist_sync_sharding", 2, 2, ["--max-steps", "2", "--transport", "nccl", "--shard", "flat",
+                                              "--reduce", "mean", "--ckpt-path", str(tmp_path / "c.pt")])
+    got, blob = load_vars(tmp_path / "c.pt")
+    want = oracle_sync_run(2, 2, reduce="mean")
+    for g, w in zip(got, want):
+        assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
+    assert blob["t"] == 2 and "adam_m" in blob and blob["adam_m"]["mnist/v8"].abs().sum() > 0
+
+
+@pytest.mark.parametrize("variant,P,transport", [("mnist_async", 1, "host"), ("mnist_async_sharding", 2, "host"),
+                                                 ("mnist_async_sharding_greedy", 2, "nccl")])
+def test_async_every_push_applied_once(tmp_path, variant, P, transport):
+    extra = ["--max-steps", "3", "--transport", transport]
+    if transport == "nccl":
+        extra += ["--ckpt-path", str(tmp_path / "c.pt")]
+    out = run_variant(variant, P, 2, extra)
+    assert len(re.findall(r"final accuracy", out)) == 2
+    if transport == "nccl":
+        _, blob = load_vars(tmp_path / "c.pt")
+        assert blob["t"] == 3 * 2          # one optimizer step per push, W pushes per round
+
+
+def test_unsharded_rejects_two_ps():
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(["bash", os.path.join(ROOT, "mnist_sync", "run.sh"), "2", "1"] + COMMON +
+                       ["--max-steps", "1"], capture_output=True, text=True, timeout=120, env=env)
+    assert r.returncode != 0 and "exactly one parameter server" in (r.stdout + r.stderr)
+
+
+def test_single_and_resume(tmp_path):
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    ck = str(tmp_path / "s.pt")
+    base = [sys.executable, "single.py"] + COMMON
+    r = subprocess.run(base + ["--max-steps", "4", "--ckpt-path", ck], cwd=os.path.join(ROOT, "mnist_sync"),
+                       capture_output=True, text=True, timeout=240, env=env)
+    assert r.returncode == 0, r.stderr
+    assert re.search(r"^epoch: 0 batch: 0 accuracy: [0-9.]+$", r.stdout, re.M)
+    assert re.search(r"^final accuracy: [0-9.]+$", r.stdout, re.M)
+    full, blob = load_vars(ck)
+    assert blob["t"] == 4 and blob["step"] == 4
+    want = oracle_sync_run(1, 4)
+    for g, w in zip(full, want):
+        assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
