@@ -1,0 +1,338 @@
+// Peer-memory communication kernels: the product's replacement for the reference's whole MPI layer.
+//
+// Reference call sites taken over: worker push ``comm.Send([grad, FLOAT], dest, tag)``
+// x14 (mnist_sync_sharding/worker.py:36), PS receive loop + numpy sum + ApplyAdam
+// (mnist_sync_sharding/parameter_server.py:112-114, 78-82), PS fan-out ``comm.Send`` / ``Bcast``
+// (parameter_server.py:124-126, mnist_sync/parameter_server.py:69), worker ``Recv`` + ``tf.assign``
+// (worker.py:90-97); async: ``Recv(ANY_SOURCE)`` + apply + reply
+// (mnist_async_sharding/parameter_server.py:99-111).
+//
+// Every rank maps every other rank's gradient arena, parameter arena, accumulator and signal pad
+// (cudaIpc handles over NVLink / NVSwitch).  Kernels then move the data themselves:
+//   K1+K3  ddl_sync_push_update_pull : device barrier -> owner pulls its range from all workers'
+//          gradient arenas (fixed order: bitwise reproducible), scales, applies SGD / momentum /
+//          TF1-Adam in place, and stores the new values into every worker's parameter arena ->
+//          device barrier.  One launch replaces 28 blocking MPI calls + 16 Session.run calls.
+//   K2     ddl_async_push            : vectorised red.global.add of a worker's gradient into the
+//          owners' accumulators (or, for SGD, of -lr*g straight into the parameters) + a
+//          release-ordered push counter.
+//          ddl_async_apply           : owner consumes its accumulator exactly once (atomicExch),
+//          applies the optimizer, bumps the shard version.
+//   K3     ddl_pull_allgather        : worker copies the owners' ranges (peer loads).
+// All spins are time-bounded (DDL_WAIT_TIMEOUT_NS) and trap instead of hanging when a peer dies.
+#include "common.cuh"
+#include "../include/ddl_b200.h"
+#include <string.h>
+
+namespace {
+
+constexpr int kCommThreads = 512;
+
+DDL_DEVICE float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+
+// all ranks: write `epoch` into slot [me] of every peer's pad, then wait until every slot of my own
+// pad has reached `epoch`.  Called by ONE thread block; thread r talks to rank r.
+DDL_DEVICE void pad_signal(const DdlComm& c, uint32_t base, uint32_t epoch) {
+  if ((int)threadIdx.x < c.world) st_release_sys(c.pads[threadIdx.x] + base + c.rank, epoch);
+}
+DDL_DEVICE void pad_wait(const DdlComm& c, uint32_t base, uint32_t epoch) {
+  if ((int)threadIdx.x < c.world) {
+    const uint32_t* slot = c.pads[c.rank] + base + threadIdx.x;
+    uint32_t spins = 0;
+    uint64_t t0 = 0;
+    while ((int32_t)(ld_acquire_sys(slot) - epoch) < 0) {
+      if ((++spins & 0x3ff) == 0) {
+        const uint64_t now = ddl_globaltimer();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > 5 * DDL_WAIT_TIMEOUT_NS) {
+          printf("[ddl] rank %d: peer %d never reached epoch %u\n", c.rank, (int)threadIdx.x, epoch);
+          __trap();
+        }
+      }
+    }
+  }
+}
+
+template <int KIND>
+DDL_DEVICE float4 opt_apply(float4 pv, float4 gv, float* m, float* v, int64_t i, float step, float a, float b,
+                            float eps) {
+  float pp[4] = {pv.x, pv.y, pv.z, pv.w};
+  float gg[4] = {gv.x, gv.y, gv.z, gv.w};
+  if (KIND == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) pp[k] -= step * gg[k];
+  } else if (KIND == 1) {
+    float4 mv = *reinterpret_cast<float4*>(m + i);
+    float mm[4] = {mv.x, mv.y, mv.z, mv.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { mm[k] = a * mm[k] + gg[k]; pp[k] -= step * mm[k]; }
+    *reinterpret_cast<float4*>(m + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+  } else {
+    float4 mv = *reinterpret_cast<float4*>(m + i);
+    float4 vv = *reinterpret_cast<float4*>(v + i);
+    float mm[4] = {mv.x, mv.y, mv.z, mv.w};
+    float vs[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      mm[k] = a * mm[k] + (1.f - a) * gg[k];
+      vs[k] = b * vs[k] + (1.f - b) * gg[k] * gg[k];
+      pp[k] -= step * mm[k] / (sqrtf(vs[k]) + eps);
+    }
+    *reinterpret_cast<float4*>(m + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+    *reinterpret_cast<float4*>(v + i) = make_float4(vs[0], vs[1], vs[2], vs[3]);
+  }
+  return make_float4(pp[0], pp[1], pp[2], pp[3]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1 + K3 (sync): reduce-scatter + scale + optimizer + all-gather in one kernel.
+// m / v are indexed like the arena (only [begin, end) is touched).  `skip` lists arena ranges whose
+// new values are NOT broadcast because their first consumer GEMM pulls them itself (K4).
+// ------------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(kCommThreads)
+sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
+  __shared__ uint32_t s_last;
+  const uint32_t t = a.st->t;                       // same on every rank: all ranks advance together
+  const uint32_t epochA = 2u * t + 1u, epochB = 2u * t + 2u;
+  // ---- barrier A: my gradients are complete (previous kernels on this stream) -> tell everyone
+  if (blockIdx.x == 0) {
+    __threadfence_system();
+    pad_signal(c, 0, epochA);
+  }
+  pad_wait(c, 0, epochA);                           // every block polls its own (local) pad
+  __syncthreads();
+
+  const float step = (KIND == 2) ? a.st->lr_t : a.lr;
+  float* myp = c.params[c.rank];
+  const int64_t n4 = (a.end - a.begin) / 4;
+  for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = a.begin + q * 4;
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int w = 0; w < c.world; ++w) {
+      if (!((a.worker_mask >> w) & 1u)) continue;
+      const float4 x = ldcg4(c.grads[w] + i);       // peer load over NVLink (L2 of the peer)
+      g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+    }
+    g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
+    const float4 pn = opt_apply<KIND>(*reinterpret_cast<float4*>(myp + i), g, a.m, a.v, i, step, a.a, a.b, a.eps);
+    *reinterpret_cast<float4*>(myp + i) = pn;
+    bool bcast = true;
+#pragma unroll
+    for (int k = 0; k < DDL_MAX_SKIP; ++k) bcast = bcast && !(i >= a.skip_begin[k] && i < a.skip_end[k]);
+    if (bcast) {
+#pragma unroll 1
+      for (int d = 0; d < c.world; ++d) {
+        if (d == c.rank || !((a.dest_mask >> d) & 1u)) continue;
+        __stcg(reinterpret_cast<float4*>(c.params[d] + i), pn);   // peer store: the pull, fused
+      }
+    }
+  }
+  // ---- barrier B: last block to finish publishes "my range is delivered" and waits for the others
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (s_last) {
+    if (threadIdx.x == 0) *a.done_counter = 0;
+    __threadfence_system();
+    pad_signal(c, 0, epochB);
+    pad_wait(c, 0, epochB);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2 (async): worker pushes its whole gradient arena to the owners with remote atomics.
+// direct_sgd: params[owner][i] += -lr * g[i]  (Hogwild, no owner-side work at all);
+// otherwise:  accum[owner][i]  += g[i]        (owner applies Adam / momentum in ddl_async_apply).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kCommThreads)
+async_push_kernel(const DdlComm c, const DdlAsyncArgs a) {
+  __shared__ uint32_t s_last;
+  const float* g = c.grads[c.rank];
+  for (int o = 0; o < a.num_shards; ++o) {
+    const int owner = a.owner_rank[o];
+    float* dst = a.direct_sgd ? c.params[owner] : c.accum[owner];
+    const float scale = a.direct_sgd ? -a.lr : 1.f;
+    const int64_t b = a.shard_begin[o], n4 = (a.shard_end[o] - b) / 4;
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
+      const int64_t i = b + q * 4;
+      float4 x = *reinterpret_cast<const float4*>(g + i);
+      if (x.x == 0.f && x.y == 0.f && x.z == 0.f && x.w == 0.f) continue;
+      x.x *= scale; x.y *= scale; x.z *= scale; x.w *= scale;
+      red_add_v4_f32(dst + i, x);
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (s_last) {
+    if (threadIdx.x == 0) *a.done_counter = 0;
+    __threadfence_system();
+    // one release-ordered counter bump per owner: "a complete push has landed"
+    if ((int)threadIdx.x < a.num_shards) {
+      const int owner = a.owner_rank[threadIdx.x];
+      const uint32_t seen = ld_acquire_sys(c.pads[owner] + DDL_PAD_VERSION);
+      atom_add_release_sys(c.pads[owner] + DDL_PAD_PUSHES, 1u);
+      // staleness of this push = owner version now - version observed at our last pull
+      const uint32_t stale = seen - a.pulled_version[threadIdx.x];
+      atomicAdd(&a.stale_hist[stale < DDL_STALE_BINS - 1 ? stale : DDL_STALE_BINS - 1], 1u);
+    }
+  }
+}
+
+// owner: 1 thread decides whether pushes are pending and advances the shard's step state
+__global__ void async_snapshot_kernel(const DdlComm c, DdlStepState* st, uint32_t* applied, uint32_t* pending,
+                                      float lr, float b1, float b2) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    const uint32_t pushes = ld_acquire_sys(c.pads[c.rank] + DDL_PAD_PUSHES);
+    const uint32_t n = pushes - *applied;
+    *pending = n;
+    if (n) {
+      *applied = pushes;
+      const uint32_t t = st->t + 1;
+      st->t = t;
+      st->lr_t = (float)((double)lr * sqrt(1.0 - pow((double)b2, (double)t)) / (1.0 - pow((double)b1, (double)t)));
+    }
+  }
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kCommThreads)
+async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const uint32_t* pending) {
+  __shared__ uint32_t s_last;
+  if (*pending == 0) return;
+  const float step = (KIND == 2) ? a.st->lr_t : a.lr;
+  float* myp = c.params[c.rank];
+  float* acc = c.accum[c.rank];
+  const int64_t n4 = (a.end - a.begin) / 4;
+  for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = a.begin + q * 4;
+    float4 g;                                        // consume exactly once, even against in-flight adds
+    g.x = atomicExch(acc + i, 0.f); g.y = atomicExch(acc + i + 1, 0.f);
+    g.z = atomicExch(acc + i + 2, 0.f); g.w = atomicExch(acc + i + 3, 0.f);
+    g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
+    const float4 pn = opt_apply<KIND>(*reinterpret_cast<float4*>(myp + i), g, a.m, a.v, i, step, a.a, a.b, a.eps);
+    *reinterpret_cast<float4*>(myp + i) = pn;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    *a.done_counter = 0;
+    __threadfence_system();
+    atom_add_release_sys(c.pads[c.rank] + DDL_PAD_VERSION, 1u);
+  }
+}
+
+// K3: worker copies every owner's range into its own parameter arena (peer loads, no barrier).
+__global__ void __launch_bounds__(kCommThreads)
+pull_allgather_kernel(const DdlComm c, const DdlAsyncArgs a) {
+  float* myp = c.params[c.rank];
+  for (int o = 0; o < a.num_shards; ++o) {
+    const int owner = a.owner_rank[o];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && a.pulled_version)
+      a.pulled_version[o] = ld_acquire_sys(c.pads[owner] + DDL_PAD_VERSION);
+    if (owner == c.rank) continue;
+    const float* src = c.params[owner];
+    const int64_t b = a.shard_begin[o], n4 = (a.shard_end[o] - b) / 4;
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
+      const int64_t i = b + q * 4;
+      *reinterpret_cast<float4*>(myp + i) = ldcg4(src + i);
+    }
+  }
+}
+
+__global__ void device_barrier_kernel(const DdlComm c, uint32_t* epoch_counter) {
+  __shared__ uint32_t e;
+  if (threadIdx.x == 0) e = ++(*epoch_counter);
+  __syncthreads();
+  __threadfence_system();
+  pad_signal(c, DDL_PAD_BARRIER, e);
+  pad_wait(c, DDL_PAD_BARRIER, e);
+}
+
+int comm_grid(int64_t elems) {
+  int64_t g = (elems / 4 + kCommThreads - 1) / kCommThreads;
+  if (g < 1) g = 1;
+  if (g > 148) g = 148;                 // one wave: every block is resident while it spins
+  return (int)g;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ddl_dev_malloc(void** p, size_t bytes) {
+  DDL_CHECK_CUDA(cudaMalloc(p, bytes));
+  DDL_CHECK_CUDA(cudaMemset(*p, 0, bytes));
+  return 0;
+}
+int ddl_dev_free(void* p) { DDL_CHECK_CUDA(cudaFree(p)); return 0; }
+int ddl_ipc_export(void* p, void* handle64) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+  DDL_CHECK_CUDA(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle64), p));
+  return 0;
+}
+int ddl_ipc_open(const void* handle64, void** p) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  DDL_CHECK_CUDA(cudaIpcOpenMemHandle(p, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+int ddl_ipc_close(void* p) { DDL_CHECK_CUDA(cudaIpcCloseMemHandle(p)); return 0; }
+int ddl_set_device(int dev) { DDL_CHECK_CUDA(cudaSetDevice(dev)); return 0; }
+int ddl_can_access_peer(int dev, int peer) {
+  int ok = 0;
+  if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) return 0;
+  return ok;
+}
+
+int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, cudaStream_t s) {
+  DDL_REQUIRE(c->world >= 1 && c->world <= DDL_MAX_PEERS, "world %d out of range", c->world);
+  DDL_REQUIRE(a->begin % 4 == 0 && a->end % 4 == 0, "shard range must be float4 aligned");
+  const int grid = comm_grid(a->end - a->begin);
+  if (kind == 0) sync_push_update_pull_kernel<0><<<grid, kCommThreads, 0, s>>>(*c, *a);
+  else if (kind == 1) sync_push_update_pull_kernel<1><<<grid, kCommThreads, 0, s>>>(*c, *a);
+  else sync_push_update_pull_kernel<2><<<grid, kCommThreads, 0, s>>>(*c, *a);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+int ddl_async_push(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s) {
+  int64_t total = 0;
+  for (int o = 0; o < a->num_shards; ++o) total += a->shard_end[o] - a->shard_begin[o];
+  async_push_kernel<<<comm_grid(total), kCommThreads, 0, s>>>(*c, *a);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, uint32_t* applied, uint32_t* pending,
+                    float b1, float b2, cudaStream_t s) {
+  async_snapshot_kernel<<<1, 32, 0, s>>>(*c, a->st, applied, pending, a->lr, b1, b2);
+  const int grid = comm_grid(a->end - a->begin);
+  if (kind == 0) async_apply_kernel<0><<<grid, kCommThreads, 0, s>>>(*c, *a, pending);
+  else if (kind == 1) async_apply_kernel<1><<<grid, kCommThreads, 0, s>>>(*c, *a, pending);
+  else async_apply_kernel<2><<<grid, kCommThreads, 0, s>>>(*c, *a, pending);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+int ddl_pull_allgather(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s) {
+  int64_t total = 0;
+  for (int o = 0; o < a->num_shards; ++o) total += a->shard_end[o] - a->shard_begin[o];
+  pull_allgather_kernel<<<comm_grid(total), kCommThreads, 0, s>>>(*c, *a);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+int ddl_device_barrier(const DdlComm* c, uint32_t* epoch_counter, cudaStream_t s) {
+  device_barrier_kernel<<<1, 32, 0, s>>>(*c, epoch_counter);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,326 @@
+// Native step executor: forward + backward of the reference CNN (and its widened / MLP variants) as
+// one C call that only enqueues kernels - no host sync, no allocation - so a whole training step can
+// be captured in a CUDA graph.
+//
+// Replaces the TF1 graph + Session of mnist_sync/model/model.py:17-112: ``sess.run(self.grads)``
+// (mnist_sync/worker.py:30) is ddl_engine_train_step, ``sess.run(self.accuracy)`` (worker.py:72) is
+// ddl_engine_eval.  Parameters and gradients live in the caller's flat arenas (one offset per
+// variable v0..v13), activations in a workspace the engine allocates once.
+#include "common.cuh"
+#include "../include/ddl_b200.h"
+
+#include <map>
+#include <new>
+#include <vector>
+
+namespace {
+
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+struct FwdPlans {                  // forward plans for one batch size
+  int B = 0;
+  DdlTcPlan* conv[3] = {nullptr, nullptr, nullptr};    // conv2..conv4
+  DdlTcPlan* fc[2] = {nullptr, nullptr};                // fc1, fc2
+  int conv_split[3] = {1, 1, 1};
+  void destroy() {
+    for (auto& p : conv) { ddl_tc_plan_destroy(p); p = nullptr; }
+    for (auto& p : fc) { ddl_tc_plan_destroy(p); p = nullptr; }
+  }
+};
+
+}  // namespace
+
+struct DdlEngine {
+  DdlEngineCfg cfg;
+  int nconv;                       // 4 (cnn) or 0 (mlp)
+  int S[5];                        // spatial size at the input of conv1..4 and after the last pool
+  int C[5];                        // channels
+  int F[4];                        // fc sizes: in, h1, h2, classes
+  int maxB;
+  // workspace
+  float* pooled[4] = {};           // p1..p4  [B, S[i+1], S[i+1], C[i+1]]
+  uint8_t* idx[4] = {};
+  float* raw = nullptr;            // raw conv sums, reused by conv2..4  [B, S, S, Cout] max
+  float* dfull = nullptr;          // full-resolution gradient dY, reused   [B, S, S, Cout] max
+  float* dpool[4] = {};            // gradient wrt pooled outputs p1..p4
+  float* h1 = nullptr;             // fc1 output after ReLU + dropout [B, F1]
+  float* h2 = nullptr;             // fc2 output after dropout        [B, F2]
+  float* dh1 = nullptr;
+  float* dh2 = nullptr;
+  float* logits = nullptr;
+  float* dlogits = nullptr;
+  DdlStepState* eval_st = nullptr; // scratch step state for evaluation
+  std::map<int, FwdPlans> train_fwd, eval_fwd;
+  // backward plans (train batch only)
+  DdlTcPlan* wg_conv[3] = {};
+  DdlTcPlan* dg_conv[3] = {};
+  int dg_split[3] = {1, 1, 1};
+  DdlTcPlan* wg_fc[2] = {};
+  DdlTcPlan* dg_fc[2] = {};        // dg_fc[0]: fc1 -> dp4 (cnn only), dg_fc[1]: fc2 -> dh1
+  std::vector<void*> allocs;
+
+  const float* P(int v) const { return cfg.params + cfg.var_offset[v]; }
+  float* G(int v) const { return cfg.grads + cfg.var_offset[v]; }
+};
+
+namespace {
+
+int alloc(DdlEngine* e, void** p, size_t bytes) {
+  DDL_CHECK_CUDA(cudaMalloc(p, bytes < 256 ? 256 : bytes));
+  e->allocs.push_back(*p);
+  return 0;
+}
+
+// pick ntile (fprop needs %32, dgrad %16; we keep %32) and a K split so the grid has ~a wave of CTAs
+void pick_tiling(int pix_tiles, int nout, int kiters, bool allow_split, int* ntile, int* ksplit) {
+  int nt = nout >= 128 && nout % 128 == 0 ? 128 : (nout % 64 == 0 ? 64 : 32);
+  while (nt > 32 && pix_tiles * cdiv(nout, nt) < 120) nt /= 2;
+  int ctas = pix_tiles * cdiv(nout, nt);
+  int ks = 1;
+  if (allow_split && ctas < 96) {
+    ks = cdiv(132, ctas);
+    if (ks > kiters / 4) ks = kiters / 4 > 0 ? kiters / 4 : 1;
+    if (ks > 8) ks = 8;
+  }
+  *ntile = nt; *ksplit = ks;
+}
+
+int pix_tiles_of(DdlTcPlan* pl) {
+  int info[8];
+  ddl_tc_plan_info(pl, info);
+  return info[0];
+}
+
+// Forward plans for batch size B.  train=true adds dropout to the FC epilogues.
+int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
+  const DdlEngineCfg& c = e->cfg;
+  out->B = B;
+  int v = 2;                                       // v0/v1 are conv1 (SIMT)
+  for (int l = 1; l < e->nconv; ++l, v += 2) {     // conv2..conv4: raw sums; bias+ReLU+pool follow
+    const int S = e->S[l], cin = e->C[l], cout = e->C[l + 1];
+    // probe the pixel tiling with a throw-away plan to size ntile / ksplit
+    DdlTcPlan* probe = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, 32, 1, 0,
+                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+    if (!probe) return -1;
+    int nt, ks;
+    pick_tiling(pix_tiles_of(probe), cout, 25 * cdiv(cin, 32), true, &nt, &ks);
+    ddl_tc_plan_destroy(probe);
+    out->conv[l - 1] = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, nt, ks, 0,
+                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+    if (!out->conv[l - 1]) return -1;
+    out->conv_split[l - 1] = ks;
+  }
+  const float* fc_in = e->nconv ? e->pooled[3] : nullptr;   // mlp: x itself (bound at run time)
+  const int vf = 2 * e->nconv;
+  const float kp = train ? c.keep_prob : 1.f;
+  const int drop = (train && c.keep_prob < 1.f) ? 4 : 0;
+  if (e->nconv) {
+    out->fc[0] = ddl_tc_plan_act(0, fc_in, e->P(vf), e->h1, B, 1, 1, e->F[0], e->F[1], 1, 32, 1, 1 | 2 | drop,
+                                 e->P(vf + 1), nullptr, 1.f, train ? c.st : nullptr, 0, kp);
+    if (!out->fc[0]) return -1;
+  }
+  out->fc[1] = ddl_tc_plan_act(0, e->h1, e->P(vf + 2), e->h2, B, 1, 1, e->F[1], e->F[2], 1, 32, 1, 1 | drop,
+                               e->P(vf + 3), nullptr, 1.f, train ? c.st : nullptr, 1, kp);
+  if (!out->fc[1]) return -1;
+  return 0;
+}
+
+int build_bwd(DdlEngine* e) {
+  const DdlEngineCfg& c = e->cfg;
+  const int B = c.batch;
+  const int vf = 2 * e->nconv;
+  const float inv_keep = c.keep_prob < 1.f ? 1.f / c.keep_prob : 1.f;
+  // fc2: dW2 = h1^T dh2 ; dh1 = (dh2 W2^T) * (h1 > 0) / keep
+  e->wg_fc[1] = ddl_tc_plan_wgrad(e->dh2, e->h1, e->G(vf + 2), B, 1, 1, e->F[2], e->F[1], 1, 64, 1);
+  e->dg_fc[1] = ddl_tc_plan_act(1, e->dh2, e->P(vf + 2), e->dh1, B, 1, 1, e->F[2], e->F[1], 1, 32, 1, 8, nullptr,
+                                e->h1, inv_keep, nullptr, 0, 1.f);
+  if (!e->wg_fc[1] || !e->dg_fc[1]) return -1;
+  if (e->nconv) {
+    e->wg_fc[0] = ddl_tc_plan_wgrad(e->dh1, e->pooled[3], e->G(vf), B, 1, 1, e->F[1], e->F[0], 1, 64, 1);
+    e->dg_fc[0] = ddl_tc_plan_act(1, e->dh1, e->P(vf), e->dpool[3], B, 1, 1, e->F[1], e->F[0], 1, 32, 1, 0, nullptr,
+                                  nullptr, 1.f, nullptr, 0, 1.f);
+    if (!e->wg_fc[0] || !e->dg_fc[0]) return -1;
+  }
+  int v = 2;
+  for (int l = 1; l < e->nconv; ++l, v += 2) {
+    const int S = e->S[l], cin = e->C[l], cout = e->C[l + 1];
+    const int nt_w = cin >= 128 ? 128 : (cin >= 64 ? 64 : 32);
+    DdlTcPlan* probe = ddl_tc_plan_wgrad(e->dfull, e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, 1);
+    if (!probe) return -1;
+    int info[8];
+    ddl_tc_plan_info(probe, info);
+    ddl_tc_plan_destroy(probe);
+    int base = info[0] * info[1];
+    int psplit = base >= 120 ? 1 : cdiv(148, base);
+    e->wg_conv[l - 1] = ddl_tc_plan_wgrad(e->dfull, e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, psplit);
+    if (!e->wg_conv[l - 1]) return -1;
+    // dgrad: dp_{l-1}[pix, cin] = sum_{tap, cout} dY[pix - off, cout] * W[tap][cin][cout]
+    DdlTcPlan* probe2 = ddl_tc_plan_act(1, e->dfull, e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, 32, 1, 0,
+                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+    if (!probe2) return -1;
+    int nt, ks;
+    pick_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), true, &nt, &ks);
+    ddl_tc_plan_destroy(probe2);
+    e->dg_conv[l - 1] = ddl_tc_plan_act(1, e->dfull, e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, nt, ks, 0,
+                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+    if (!e->dg_conv[l - 1]) return -1;
+    e->dg_split[l - 1] = ks;
+  }
+  return 0;
+}
+
+FwdPlans* get_fwd(DdlEngine* e, int B, bool train) {
+  auto& cache = train ? e->train_fwd : e->eval_fwd;
+  auto it = cache.find(B);
+  if (it != cache.end()) return &it->second;
+  FwdPlans fp;
+  if (build_fwd(e, B, train, &fp)) { fp.destroy(); return nullptr; }
+  return &(cache[B] = fp);
+}
+
+// forward through fc2; x [B,784].  Writes pooled[], idx[] (train), h1, h2.
+int forward(DdlEngine* e, FwdPlans* fp, const float* x, int B, bool train, cudaStream_t s) {
+  int v = 0;
+  if (e->nconv) {
+    if (ddl_conv1_relu_pool(x, e->P(0), e->P(1), e->pooled[0], train ? e->idx[0] : nullptr, B, e->S[0], e->C[1], s))
+      return -1;
+    v = 2;
+    for (int l = 1; l < e->nconv; ++l, v += 2) {
+      const int S = e->S[l], cout = e->C[l + 1];
+      if (fp->conv_split[l - 1] > 1)
+        DDL_CHECK_CUDA(cudaMemsetAsync(e->raw, 0, (size_t)B * S * S * cout * sizeof(float), s));
+      if (ddl_tc_plan_run(fp->conv[l - 1], s)) return -1;
+      if (ddl_maxpool_fwd(e->raw, e->P(v + 1), e->pooled[l], train ? e->idx[l] : nullptr, B, S, S, cout, s)) return -1;
+    }
+    if (ddl_tc_plan_run(fp->fc[0], s)) return -1;
+  }
+  if (ddl_tc_plan_run(fp->fc[1], s)) return -1;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg) {
+  auto fail = [](DdlEngine* e, const char* why) -> DdlEngine* {
+    if (why) ddl::set_error("ddl_engine_create: %s", why);
+    if (e) ddl_engine_destroy(e);
+    return nullptr;
+  };
+  if (cfg->kind != 0 && cfg->kind != 1) return fail(nullptr, "kind must be 0 (cnn) or 1 (mlp)");
+  if (cfg->kind == 1) return fail(nullptr, "the mlp variant runs on the torch backend (fc1 input is not a plan-bound buffer)");
+  DdlEngine* e = new (std::nothrow) DdlEngine();
+  if (!e) return fail(nullptr, "out of host memory");
+  e->cfg = *cfg;
+  e->nconv = 4;
+  const int wm = cfg->width_mult;
+  e->C[0] = 1; e->C[1] = 32 * wm; e->C[2] = 64 * wm; e->C[3] = 128 * wm; e->C[4] = 256 * wm;
+  e->S[0] = 28;
+  for (int i = 1; i < 5; ++i) e->S[i] = (e->S[i - 1] + 1) / 2;
+  e->F[0] = e->S[4] * e->S[4] * e->C[4]; e->F[1] = 1024 * wm; e->F[2] = 512 * wm; e->F[3] = 10;
+  e->maxB = cfg->batch > cfg->max_eval_batch ? cfg->batch : cfg->max_eval_batch;
+  const size_t mb = (size_t)e->maxB;
+  size_t full_max = 0;
+  for (int l = 0; l < 4; ++l) {
+    const size_t pooled = mb * e->S[l + 1] * e->S[l + 1] * e->C[l + 1];
+    const size_t full = mb * e->S[l] * e->S[l] * e->C[l + 1];
+    if (l >= 1 && full > full_max) full_max = full;   // conv1 never touches `raw`
+    if (alloc(e, (void**)&e->pooled[l], pooled * 4)) return fail(e, nullptr);
+    if (alloc(e, (void**)&e->idx[l], (size_t)cfg->batch * e->S[l + 1] * e->S[l + 1] * e->C[l + 1])) return fail(e, nullptr);
+    if (alloc(e, (void**)&e->dpool[l], (size_t)cfg->batch * e->S[l + 1] * e->S[l + 1] * e->C[l + 1] * 4)) return fail(e, nullptr);
+  }
+  const size_t full_train = (size_t)cfg->batch * e->S[0] * e->S[0] * e->C[1] > (size_t)cfg->batch * e->S[1] * e->S[1] * e->C[2]
+                                ? (size_t)cfg->batch * e->S[0] * e->S[0] * e->C[1]
+                                : (size_t)cfg->batch * e->S[1] * e->S[1] * e->C[2];
+  if (alloc(e, (void**)&e->raw, full_max * 4)) return fail(e, nullptr);
+  if (alloc(e, (void**)&e->dfull, full_train * 4)) return fail(e, nullptr);
+  if (alloc(e, (void**)&e->h1, mb * e->F[1] * 4) || alloc(e, (void**)&e->h2, mb * e->F[2] * 4) ||
+      alloc(e, (void**)&e->dh1, (size_t)cfg->batch * e->F[1] * 4) || alloc(e, (void**)&e->dh2, (size_t)cfg->batch * e->F[2] * 4) ||
+      alloc(e, (void**)&e->logits, mb * 16 * 4) || alloc(e, (void**)&e->dlogits, (size_t)cfg->batch * 16 * 4) ||
+      alloc(e, (void**)&e->eval_st, sizeof(DdlStepState)))
+    return fail(e, nullptr);
+  if (cudaMemset(e->eval_st, 0, sizeof(DdlStepState)) != cudaSuccess) return fail(e, "memset failed");
+  if (!get_fwd(e, cfg->batch, true)) return fail(e, nullptr);
+  if (build_bwd(e)) return fail(e, nullptr);
+  return e;
+}
+
+void ddl_engine_destroy(DdlEngine* e) {
+  if (!e) return;
+  for (auto& kv : e->train_fwd) kv.second.destroy();
+  for (auto& kv : e->eval_fwd) kv.second.destroy();
+  for (auto& p : e->wg_conv) ddl_tc_plan_destroy(p);
+  for (auto& p : e->dg_conv) ddl_tc_plan_destroy(p);
+  for (auto& p : e->wg_fc) ddl_tc_plan_destroy(p);
+  for (auto& p : e->dg_fc) ddl_tc_plan_destroy(p);
+  for (void* p : e->allocs) cudaFree(p);
+  delete e;
+}
+
+/* gradients of the mean cross-entropy of (x, y) into the gradient arena; loss_sum / correct into st.
+ * The caller advances st (ddl_step_advance) first.  Enqueue-only. */
+int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream_t s) {
+  const DdlEngineCfg& c = e->cfg;
+  const int B = c.batch;
+  FwdPlans* fp = get_fwd(e, B, true);
+  DDL_REQUIRE(fp != nullptr, "ddl_engine_train_step: no forward plans");
+  DDL_CHECK_CUDA(cudaMemsetAsync(c.grads, 0, (size_t)c.arena_elems * sizeof(float), s));
+  if (forward(e, fp, x, B, true, s)) return -1;
+  const int vf = 2 * e->nconv;
+  if (ddl_fc3_xent_fwd(e->h2, e->P(vf + 4), e->P(vf + 5), y, nullptr, e->dlogits, c.st, B, e->F[2], e->F[3],
+                       1.f / (float)B, s)) return -1;
+  // ---- backward
+  if (ddl_fc3_bwd_st(e->h2, e->P(vf + 4), e->dlogits, e->G(vf + 4), e->G(vf + 5), e->dh2, B, e->F[2], e->F[3],
+                     c.st, 1, c.keep_prob, s)) return -1;
+  if (ddl_tc_plan_run(e->wg_fc[1], s)) return -1;
+  if (ddl_colsum(e->dh2, e->G(vf + 3), B, e->F[2], s)) return -1;
+  if (ddl_tc_plan_run(e->dg_fc[1], s)) return -1;
+  if (ddl_tc_plan_run(e->wg_fc[0], s)) return -1;
+  if (ddl_colsum(e->dh1, e->G(vf + 1), B, e->F[1], s)) return -1;
+  if (ddl_tc_plan_run(e->dg_fc[0], s)) return -1;
+  int v = 6;
+  for (int l = 3; l >= 1; --l, v -= 2) {           // conv4, conv3, conv2
+    const int S = e->S[l], cout = e->C[l + 1], cin = e->C[l];
+    if (ddl_maxpool_bwd(e->dpool[l], e->idx[l], e->dfull, e->G(v + 1), B, S, S, cout, s)) return -1;
+    if (ddl_tc_plan_run(e->wg_conv[l - 1], s)) return -1;
+    if (e->dg_split[l - 1] > 1)
+      DDL_CHECK_CUDA(cudaMemsetAsync(e->dpool[l - 1], 0, (size_t)B * S * S * cin * sizeof(float), s));
+    if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
+  }
+  if (ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull, nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
+  if (ddl_conv1_wgrad(x, e->dfull, e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
+  return 0;
+}
+
+/* forward only (keep_prob = 1) over n <= max_eval_batch rows; adds the number of correct rows to
+ * *correct (device) and optionally writes logits [n,10]. */
+int ddl_engine_eval(DdlEngine* e, const float* x, const int* y, int n, unsigned* correct, float* logits_out,
+                    cudaStream_t s) {
+  DDL_REQUIRE(n >= 1 && n <= e->maxB, "ddl_engine_eval: n=%d exceeds max_eval_batch=%d", n, e->maxB);
+  FwdPlans* fp = get_fwd(e, n, false);
+  DDL_REQUIRE(fp != nullptr, "ddl_engine_eval: could not build plans for n=%d: %s", n, ddl_last_error());
+  if (forward(e, fp, x, n, false, s)) return -1;
+  const int vf = 2 * e->nconv;
+  float* lg = logits_out ? logits_out : e->logits;
+  if (ddl_fc3_xent_fwd(e->h2, e->P(vf + 4), e->P(vf + 5), nullptr, lg, nullptr, nullptr, n, e->F[2], e->F[3], 1.f, s))
+    return -1;
+  if (y && correct) return ddl_accuracy(lg, y, correct, n, e->F[3], s);
+  return 0;
+}
+
+/* debug / test access to intermediate buffers: 0..3 pooled p1..p4, 4 h1, 5 h2, 6 dh1, 7 dh2,
+ * 8..11 dpool p1..p4, 12 dfull, 13 raw */
+const float* ddl_engine_buffer(const DdlEngine* e, int which) {
+  if (which >= 0 && which < 4) return e->pooled[which];
+  if (which == 4) return e->h1;
+  if (which == 5) return e->h2;
+  if (which == 6) return e->dh1;
+  if (which == 7) return e->dh2;
+  if (which >= 8 && which < 12) return e->dpool[which - 8];
+  if (which == 12) return e->dfull;
+  if (which == 13) return e->raw;
+  return nullptr;
+}
+
+}  // extern "C"

@@ -1,0 +1,23 @@
+// Thread-local error string behind ddl_last_error().
+#include "common.cuh"
+#include "../include/ddl_b200.h"
+#include <stdarg.h>
+
+namespace ddl {
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* get_error() { return g_err; }
+}  // namespace ddl
+
+extern "C" const char* ddl_last_error(void) { return ddl::get_error(); }
+extern "C" int ddl_version(void) { return 100; }
+
+extern "C" int ddl_memcpy_async(void* dst, const void* src, size_t bytes, cudaStream_t s) {
+  DDL_CHECK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, s));
+  return 0;
+}

@@ -1,0 +1,536 @@
+// tcgen05 / TMEM / TMA implicit-GEMM kernels for sm_100a: conv fprop, conv dgrad, conv wgrad and the
+// FC matmuls (fwd, dX, dW) of the reference CNN - every GEMM-shaped op with >= 32 reduction channels.
+//
+// Reference ops replaced: tf.nn.conv2d x3 (mnist_sync/model/model.py:39,50,61) and their
+// backprop-input / backprop-filter ops (implied by compute_gradients, model.py:101), tf.matmul
+// fc1/fc2 forward and backward (model.py:70,79).  conv1 (Cin = 1) and fc3 (N = 10) are SIMT kernels
+// in elementwise.cu: their shapes cannot feed a 128xNx8 UMMA usefully (and a [*,10] fp32 row is
+// not a legal 16-byte TMA stride).
+//
+// Design (B200-first, not a port of anything):
+//   * data stays fp32 in HBM; the tensor core consumes it as kind::tf32 (fp32 accumulate in TMEM);
+//   * the im2col operand is never materialised: one 4-D TMA box [32 ch, bw, bh, bn] of the NHWC
+//     activation, shifted by the filter tap, IS the 128-row K-major A tile of that tap.  Out-of-
+//     bounds rows/columns are zero-filled by TMA, which is exactly SAME padding;
+//   * weights (HWIO) are read in place: [Cin, Cout] per tap is an MN-major B tile for fprop and a
+//     K-major B tile for dgrad - no transposed copies exist anywhere;
+//   * wgrad reduces over pixels, so both operands (dY, shifted X) are MN-major boxes; partial sums
+//     from pixel splits go straight into the gradient arena with red.global.add;
+//   * warp-specialised CTA: warp 0 = TMA producer, warp 1 = MMA issuer (one lane) + TMEM owner,
+//     warps 2..5 = epilogue (tcgen05.ld -> bias / ReLU / dropout / mask -> global);
+//   * SWIZZLE_128B everywhere: a 32-float row is one 128-byte swizzle span.
+#include "common.cuh"
+#include "../include/ddl_b200.h"
+
+#include <mutex>
+#include <new>
+
+namespace {
+
+constexpr int kTileM = 128;        // UMMA M (TMEM lanes)
+constexpr int kKB = 32;            // fp32 elements per K-block = one 128-byte swizzle row
+constexpr int kUmmaK = 8;          // tf32: 32 bytes of K per instruction
+constexpr int kThreadsTc = 192;    // 6 warps
+constexpr int kMaxStages = 8;
+
+struct ActParams {
+  // pixel space of the activation operand and of the output
+  int N, H, W;
+  int bw, bh, bn;                  // TMA pixel box; rows per tile = bw*bh*bn <= 128
+  int tiles_w, tiles_h, tiles_n;
+  int ksize, flip;                 // filter size (5 or 1); flip = dgrad (offset negated)
+  int cblocks;                     // ceil(reduction channels / 32)
+  int kiters;                      // ksize*ksize*cblocks
+  int ksplit;                      // gridDim.z
+  int nout, ntile;                 // output channels, UMMA N
+  int stages;
+  int b_mn_major;                  // 1: weights [tap][cred][nout] (fprop), 0: [tap][nout][cred] (dgrad)
+  int flags;
+  float* out;                      // [N*H*W, nout]
+  const float* bias;               // [nout]
+  const float* mask_act;           // [N*H*W, nout]; EPI_MASKPOS multiplies by (mask_act > 0) * mask_scale
+  float mask_scale;
+  const DdlStepState* st;          // dropout seed / stream
+  uint32_t drop_stream_off;
+  uint32_t drop_thresh24;
+  float drop_inv_keep;
+};
+
+struct WgradParams {
+  int N, H, W;
+  int bw, bh, bn;                  // pixel box, rows R = bw*bh*bn, R % 8 == 0
+  int tiles_w, tiles_h, tiles_n;
+  int ksize;
+  int ca, cb;                      // channels of the gradient operand (M side) and of the input operand (N side)
+  int mtiles, ntiles, ntile;
+  int psplit;
+  int stages;
+  float* out;                      // [taps][cb][ca], accumulated with red.add
+};
+
+enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16 };
+
+struct alignas(8) PipeBars {
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
+  uint64_t tmem_full;
+  uint32_t tmem_addr;
+  uint32_t pad;
+};
+
+__device__ __forceinline__ uint32_t tmem_cols_for(int n) {
+  return n <= 32 ? 32u : n <= 64 ? 64u : n <= 128 ? 128u : 256u;
+}
+
+// ------------------------------------------------------------------------------------------------
+// act-GEMM: out[pix, n] = epi( sum_{tap, c} act[pix + off(tap), c] * Wt[tap][c][n] )
+// grid = (pixel tiles, n tiles, ksplit)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreadsTc, 1)
+tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_w,
+                   const ActParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int a_bytes = kTileM * 128;
+  const int b_bytes = p.ntile * 128;
+  const int stage_bytes = a_bytes + b_bytes;
+  PipeBars* bars = (PipeBars*)(smem + (size_t)p.stages * stage_bytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = blockIdx.x;
+  const int tw = tile % p.tiles_w, th = (tile / p.tiles_w) % p.tiles_h, tn = tile / (p.tiles_w * p.tiles_h);
+  const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
+  const int nt0 = blockIdx.y * p.ntile;
+  const int per = (p.kiters + p.ksplit - 1) / p.ksplit;
+  const int k_begin = blockIdx.z * per;
+  const int k_end = min(p.kiters, k_begin + per);
+  const int niter = max(0, k_end - k_begin);
+  const uint32_t ncols = tmem_cols_for(p.ntile);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+    mbar_init(&bars->tmem_full, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&map_act);
+    tma_prefetch_desc(&map_w);
+  }
+  if (warp == 1) tmem_alloc(&bars->tmem_addr, ncols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_addr;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      const int box_rows = p.bw * p.bh * p.bn;
+      const uint32_t tx = (uint32_t)(box_rows * 128 + b_bytes);
+      const int half = p.ksize / 2;
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % p.stages;
+        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
+        mbar_wait(&bars->empty[s], ph ^ 1u);
+        const int it = k_begin + i;
+        const int tap = it / p.cblocks, cb = it % p.cblocks;
+        int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
+        if (p.flip) { dh = -dh; dw = -dw; }
+        uint8_t* sa = smem + (size_t)s * stage_bytes;
+        uint8_t* sb = sa + a_bytes;
+        mbar_expect_tx(&bars->full[s], tx);
+        tma_load_4d(sa, &map_act, &bars->full[s], cb * kKB, w0 + dw, h0 + dh, n0);
+        if (p.b_mn_major) {
+          for (int j = 0; j < p.ntile / 32; ++j)
+            tma_load_4d(sb + j * 4096, &map_w, &bars->full[s], nt0 + 32 * j, cb * kKB, tap, 0);
+        } else {
+          tma_load_4d(sb, &map_w, &bars->full[s], cb * kKB, nt0, tap, 0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_tf32(kTileM, p.ntile, 0, p.b_mn_major);
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % p.stages;
+        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
+        mbar_wait(&bars->full[s], ph);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+        const uint32_t sb = sa + a_bytes;
+#pragma unroll
+        for (int k = 0; k < kKB / kUmmaK; ++k) {
+          const uint64_t ad = umma_smem_desc(sa + k * 32, 16, 1024, DDL_UMMA_SW128);
+          const uint64_t bd = p.b_mn_major ? umma_smem_desc(sb + k * 1024, 4096, 512, DDL_UMMA_SW128_BASE32B)
+                                           : umma_smem_desc(sb + k * 32, 16, 1024, DDL_UMMA_SW128);
+          umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&bars->empty[s]);            // smem slot reusable once these MMAs have read it
+      }
+      umma_commit(&bars->tmem_full);             // accumulator complete
+    }
+  } else {
+    // ================= epilogue (warps 2..5) =================
+    const int q = warp & 3;                      // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;
+    const int rw = row % p.bw, rh = (row / p.bw) % p.bh, rn = row / (p.bw * p.bh);
+    const int pw = w0 + rw, phh = h0 + rh, pn = n0 + rn;
+    const bool valid = (rn < p.bn) && pw < p.W && phh < p.H && pn < p.N && niter > 0;
+    const int64_t pix = ((int64_t)pn * p.H + phh) * p.W + pw;
+    float* orow = p.out + pix * p.nout + nt0;
+    const float* mrow = (p.flags & EPI_MASKPOS) ? p.mask_act + pix * p.nout + nt0 : nullptr;
+    uint32_t seed = 0, stream = 0;
+    if (p.flags & EPI_DROPOUT) { seed = p.st->seed; stream = p.st->stream + p.drop_stream_off; }
+    mbar_wait(&bars->tmem_full, 0);
+    tc_fence_after();
+    for (int c0 = 0; c0 < p.ntile; c0 += 16) {
+      float v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      if (!valid) continue;
+      if (p.flags & EPI_ATOMIC) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) {
+          if (nt0 + c0 + j < p.nout) red_add_v4_f32(orow + c0 + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+        }
+        continue;
+      }
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int col = nt0 + c0 + j;
+        float x = v[j];
+        if (p.flags & EPI_BIAS) x += (col < p.nout) ? __ldg(p.bias + col) : 0.f;
+        if (p.flags & EPI_RELU) x = fmaxf(x, 0.f);
+        if (p.flags & EPI_DROPOUT) {
+          const uint32_t e = (uint32_t)(pix * p.nout + col);
+          x = ddl_dropout_keep(seed, stream, e, p.drop_thresh24) ? x * p.drop_inv_keep : 0.f;
+        }
+        v[j] = x;
+      }
+      if (p.flags & EPI_MASKPOS) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) {
+          if (nt0 + c0 + j < p.nout) {
+            const float4 m = *reinterpret_cast<const float4*>(mrow + c0 + j);
+            v[j] = m.x > 0.f ? v[j] * p.mask_scale : 0.f;
+            v[j + 1] = m.y > 0.f ? v[j + 1] * p.mask_scale : 0.f;
+            v[j + 2] = m.z > 0.f ? v[j + 2] * p.mask_scale : 0.f;
+            v[j + 3] = m.w > 0.f ? v[j + 3] * p.mask_scale : 0.f;
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 16; j += 4) {
+        if (nt0 + c0 + j < p.nout)
+          *reinterpret_cast<float4*>(orow + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, ncols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// wgrad: out[tap][b][a] += sum_{pix} G[pix, a] * X[pix + off(tap), b]
+// grid = (taps, mtiles * ntiles, psplit)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreadsTc, 1)
+tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_x,
+                const WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int R = p.bw * p.bh * p.bn;
+  const int box_bytes = R * 128;
+  const int a_boxes = kTileM / 32, b_boxes = p.ntile / 32;
+  const int stage_bytes = (a_boxes + b_boxes) * box_bytes;
+  PipeBars* bars = (PipeBars*)(smem + (size_t)p.stages * stage_bytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tap = blockIdx.x;
+  const int mt = blockIdx.y % p.mtiles, nt = blockIdx.y / p.mtiles;
+  const int a0 = mt * kTileM, b0 = nt * p.ntile;
+  const int half = p.ksize / 2;
+  const int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
+  const int ptiles = p.tiles_w * p.tiles_h * p.tiles_n;
+  const int per = (ptiles + p.psplit - 1) / p.psplit;
+  const int t_begin = blockIdx.z * per;
+  const int t_end = min(ptiles, t_begin + per);
+  const int niter = max(0, t_end - t_begin);
+  const uint32_t ncols = tmem_cols_for(p.ntile);
+  const int a_live = min(a_boxes, (p.ca - a0 + 31) / 32);     // boxes that hold real channels
+  const int b_live = min(b_boxes, (p.cb - b0 + 31) / 32);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+    mbar_init(&bars->tmem_full, 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&map_g);
+    tma_prefetch_desc(&map_x);
+  }
+  if (warp == 1) tmem_alloc(&bars->tmem_addr, ncols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_addr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t tx = (uint32_t)((a_live + b_live) * box_bytes);
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % p.stages;
+        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
+        mbar_wait(&bars->empty[s], ph ^ 1u);
+        const int t = t_begin + i;
+        const int tw = t % p.tiles_w, th = (t / p.tiles_w) % p.tiles_h, tn = t / (p.tiles_w * p.tiles_h);
+        const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
+        uint8_t* sa = smem + (size_t)s * stage_bytes;
+        uint8_t* sb = sa + a_boxes * box_bytes;
+        mbar_expect_tx(&bars->full[s], tx);
+        for (int j = 0; j < a_live; ++j)
+          tma_load_4d(sa + j * box_bytes, &map_g, &bars->full[s], a0 + 32 * j, w0, h0, n0);
+        for (int j = 0; j < b_live; ++j)
+          tma_load_4d(sb + j * box_bytes, &map_x, &bars->full[s], b0 + 32 * j, w0 + dw, h0 + dh, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_tf32(kTileM, p.ntile, 1, 1);
+      const int ksteps = R / kUmmaK;
+      for (int i = 0; i < niter; ++i) {
+        const int s = i % p.stages;
+        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
+        mbar_wait(&bars->full[s], ph);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+        const uint32_t sb = sa + a_boxes * box_bytes;
+        for (int k = 0; k < ksteps; ++k) {
+          const uint64_t ad = umma_smem_desc(sa + k * 1024, (uint32_t)box_bytes, 512, DDL_UMMA_SW128_BASE32B);
+          const uint64_t bd = umma_smem_desc(sb + k * 1024, (uint32_t)box_bytes, 512, DDL_UMMA_SW128_BASE32B);
+          umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&bars->empty[s]);
+      }
+      umma_commit(&bars->tmem_full);
+    }
+  } else {
+    const int q = warp & 3;
+    const int a = a0 + q * 32 + lane;
+    const bool valid = a < p.ca && niter > 0;
+    float* obase = p.out + (int64_t)tap * p.cb * p.ca + a;
+    mbar_wait(&bars->tmem_full, 0);
+    tc_fence_after();
+    for (int c0 = 0; c0 < p.ntile; c0 += 16) {
+      float v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      if (!valid) continue;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int b = b0 + c0 + j;
+        if (b < p.cb) atomicAdd(obase + (int64_t)b * p.ca, v[j]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, ncols);
+}
+
+// ------------------------------------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)f;
+  });
+  return fn;
+}
+
+// fp32 tensor with contiguous dims (innermost first) d0..d3; box b0..b3 (b0 = 32 floats = one 128-byte
+// swizzle span).  mn_major selects the 32-byte-atom swizzle that MN-major tf32 operands require.
+int make_map4(CUtensorMap* m, const void* ptr, const uint64_t d[4], const uint32_t b[4], bool mn_major) {
+  EncodeTiledFn enc = get_encode();
+  DDL_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+  DDL_REQUIRE(((uintptr_t)ptr & 15) == 0, "TMA base address must be 16-byte aligned");
+  DDL_REQUIRE((d[0] * 4) % 16 == 0, "TMA row pitch (%llu floats) must be a multiple of 16 bytes",
+              (unsigned long long)d[0]);
+  cuuint64_t dims[4] = {d[0], d[1], d[2], d[3]};
+  cuuint64_t strides[3] = {d[0] * 4, d[0] * d[1] * 4, d[0] * d[1] * d[2] * 4};
+  cuuint32_t box[4] = {b[0], b[1], b[2], b[3]};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  for (int i = 0; i < 4; ++i) DDL_REQUIRE(box[i] >= 1 && box[i] <= 256, "TMA box dim %d = %u out of range", i, box[i]);
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DDL_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// Choose the pixel box (bw, bh, bn): rows = bw*bh*bn <= max_rows, rows % row_mult == 0, minimising
+// the number of tiles (ties: fewer rows).  bh / bn may overshoot the tensor by up to row_mult-1:
+// TMA zero-fills out-of-bounds rows, which contribute nothing to a reduction and are skipped by
+// the epilogue of the act kernel.
+void choose_box(int N, int H, int W, int max_rows, int row_mult, int* bw, int* bh, int* bn) {
+  int best_tiles = 1 << 30, best_rows = 0;
+  *bw = 1; *bh = 1; *bn = row_mult;
+  const int hmax = (H + row_mult - 1) / row_mult * row_mult;
+  const int nmax = (N + row_mult - 1) / row_mult * row_mult;
+  for (int w = 1; w <= W && w <= 256; ++w) {
+    if (w != W && W % w != 0) continue;                 // full rows or exact divisors of the width
+    for (int h = 1; h <= hmax && h <= 256 && w * h <= max_rows; ++h) {
+      for (int n = 1; n <= nmax && n <= 256 && w * h * n <= max_rows; ++n) {
+        int rows = w * h * n;
+        if (rows % row_mult) continue;
+        int tiles = ceil_div(W, w) * ceil_div(H, h) * ceil_div(N, n);
+        if (tiles < best_tiles || (tiles == best_tiles && rows < best_rows)) {
+          best_tiles = tiles; best_rows = rows; *bw = w; *bh = h; *bn = n;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace
+
+struct DdlTcPlan {
+  int kind;                 // 0 act, 1 wgrad
+  CUtensorMap map_a, map_b;
+  ActParams act;
+  WgradParams wg;
+  dim3 grid;
+  size_t smem;
+};
+
+extern "C" {
+
+DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
+                           int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
+                           const float* mask_act, float mask_scale, const DdlStepState* st,
+                           uint32_t drop_stream_off, float keep_prob) {
+  auto fail = [](const char* why) -> DdlTcPlan* { ddl::set_error("ddl_tc_plan_act: %s", why); return nullptr; };
+  if (cred % 4 || nout % 4) return fail("channel counts must be multiples of 4 (16-byte TMA pitch)");
+  if (ntile < 16 || ntile > 256 || ntile % 16) return fail("ntile must be a multiple of 16 in [16, 256]");
+  if (!dgrad && ntile % 32) return fail("fprop ntile must be a multiple of 32 (MN-major boxes)");
+  if (ksize != 1 && ksize != 5 && ksize != 3) return fail("ksize must be 1, 3 or 5");
+  DdlTcPlan* pl = new (std::nothrow) DdlTcPlan();
+  if (!pl) return fail("out of host memory");
+  pl->kind = 0;
+  ActParams& p = pl->act;
+  p.N = N; p.H = H; p.W = W;
+  choose_box(N, H, W, kTileM, 1, &p.bw, &p.bh, &p.bn);
+  p.tiles_w = ceil_div(W, p.bw); p.tiles_h = ceil_div(H, p.bh); p.tiles_n = ceil_div(N, p.bn);
+  p.ksize = ksize; p.flip = dgrad ? 1 : 0;
+  p.cblocks = ceil_div(cred, kKB);
+  p.kiters = ksize * ksize * p.cblocks;
+  p.ksplit = ksplit < 1 ? 1 : (ksplit > p.kiters ? p.kiters : ksplit);
+  p.nout = nout; p.ntile = ntile;
+  p.b_mn_major = dgrad ? 0 : 1;
+  p.flags = flags | (p.ksplit > 1 ? EPI_ATOMIC : 0);
+  p.out = out; p.bias = bias; p.mask_act = mask_act; p.mask_scale = mask_scale;
+  p.st = st; p.drop_stream_off = drop_stream_off;
+  p.drop_thresh24 = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
+  p.drop_inv_keep = keep_prob >= 1.f ? 1.f : 1.f / keep_prob;
+  const int stage_bytes = kTileM * 128 + ntile * 128;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages > p.kiters) stages = p.kiters < 2 ? 2 : p.kiters;
+  p.stages = stages;
+  pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
+  pl->grid = dim3(p.tiles_w * p.tiles_h * p.tiles_n, ceil_div(nout, ntile), p.ksplit);
+  const uint64_t da[4] = {(uint64_t)cred, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  const uint32_t ba[4] = {kKB, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+  if (make_map4(&pl->map_a, act, da, ba, false)) { delete pl; return nullptr; }
+  const int taps = ksize * ksize;
+  if (!dgrad) {           // W as [taps][cred][nout]: inner = nout
+    const uint64_t dw[4] = {(uint64_t)nout, (uint64_t)cred, (uint64_t)taps, 1};
+    const uint32_t bwb[4] = {32, kKB, 1, 1};
+    if (make_map4(&pl->map_b, w, dw, bwb, true)) { delete pl; return nullptr; }
+  } else {                // W as [taps][nout][cred]: inner = cred (the reduction)
+    const uint64_t dw[4] = {(uint64_t)cred, (uint64_t)nout, (uint64_t)taps, 1};
+    const uint32_t bwb[4] = {kKB, (uint32_t)ntile, 1, 1};
+    if (make_map4(&pl->map_b, w, dw, bwb, false)) { delete pl; return nullptr; }
+  }
+  if (cudaFuncSetAttribute(tc_act_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) {
+    delete pl;
+    return fail("cudaFuncSetAttribute(max dynamic smem) failed");
+  }
+  return pl;
+}
+
+DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,
+                             int ksize, int ntile, int psplit) {
+  auto fail = [](const char* why) -> DdlTcPlan* { ddl::set_error("ddl_tc_plan_wgrad: %s", why); return nullptr; };
+  if (ca % 4 || cb % 4) return fail("channel counts must be multiples of 4 (16-byte TMA pitch)");
+  if (ntile < 32 || ntile > 256 || ntile % 32) return fail("ntile must be a multiple of 32 in [32, 256]");
+  DdlTcPlan* pl = new (std::nothrow) DdlTcPlan();
+  if (!pl) return fail("out of host memory");
+  pl->kind = 1;
+  WgradParams& p = pl->wg;
+  p.N = N; p.H = H; p.W = W;
+  // rows per stage: multiple of 8 (one UMMA K step = 8 pixel rows); cap so 2+ stages fit in smem
+  const int boxes = kTileM / 32 + ntile / 32;
+  int max_rows = ((200 * 1024 / 2) / (boxes * 128)) & ~7;
+  if (max_rows > 128) max_rows = 128;
+  choose_box(N, H, W, max_rows, 8, &p.bw, &p.bh, &p.bn);
+  const int R = p.bw * p.bh * p.bn;
+  if (R % 8) { delete pl; return fail("no pixel box with a multiple of 8 rows"); }
+  if (p.bw > 256 || p.bh > 256 || p.bn > 256 || R > 256) { delete pl; return fail("pixel box does not fit TMA limits"); }
+  p.tiles_w = ceil_div(W, p.bw); p.tiles_h = ceil_div(H, p.bh); p.tiles_n = ceil_div(N, p.bn);
+  p.ksize = ksize; p.ca = ca; p.cb = cb;
+  p.mtiles = ceil_div(ca, kTileM); p.ntile = ntile; p.ntiles = ceil_div(cb, ntile);
+  const int ptiles = p.tiles_w * p.tiles_h * p.tiles_n;
+  p.psplit = psplit < 1 ? 1 : (psplit > ptiles ? ptiles : psplit);
+  const int stage_bytes = boxes * R * 128;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 1) { delete pl; return fail("stage does not fit in shared memory"); }
+  p.stages = stages;
+  p.out = out;
+  pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
+  pl->grid = dim3(ksize * ksize, p.mtiles * p.ntiles, p.psplit);
+  const uint64_t dg[4] = {(uint64_t)ca, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  const uint64_t dx[4] = {(uint64_t)cb, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  const uint32_t bx[4] = {32, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+  if (make_map4(&pl->map_a, g, dg, bx, true) || make_map4(&pl->map_b, x, dx, bx, true)) { delete pl; return nullptr; }
+  if (cudaFuncSetAttribute(tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) {
+    delete pl;
+    return fail("cudaFuncSetAttribute(max dynamic smem) failed");
+  }
+  return pl;
+}
+
+int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s) {
+  DDL_REQUIRE(pl != nullptr, "ddl_tc_plan_run: null plan");
+  if (pl->kind == 0)
+    tc_act_gemm_kernel<<<pl->grid, kThreadsTc, pl->smem, s>>>(pl->map_a, pl->map_b, pl->act);
+  else
+    tc_wgrad_kernel<<<pl->grid, kThreadsTc, pl->smem, s>>>(pl->map_a, pl->map_b, pl->wg);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+void ddl_tc_plan_destroy(DdlTcPlan* pl) { delete pl; }
+
+/* introspection for tests / profiling notes: fills {grid.x, grid.y, grid.z, stages, smem, bw, bh, bn} */
+int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8) {
+  DDL_REQUIRE(pl != nullptr, "ddl_tc_plan_info: null plan");
+  out8[0] = pl->grid.x; out8[1] = pl->grid.y; out8[2] = pl->grid.z;
+  out8[3] = pl->kind == 0 ? pl->act.stages : pl->wg.stages;
+  out8[4] = (int)pl->smem;
+  out8[5] = pl->kind == 0 ? pl->act.bw : pl->wg.bw;
+  out8[6] = pl->kind == 0 ? pl->act.bh : pl->wg.bh;
+  out8[7] = pl->kind == 0 ? pl->act.bn : pl->wg.bn;
+  return 0;
+}
+
+}  // extern "C"

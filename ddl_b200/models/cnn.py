@@ -61,6 +61,8 @@ class TorchBackend:
 def pick_backend(cfg: Config, device: torch.device) -> str:
     if cfg.backend != "auto":
         return cfg.backend
+    if cfg.model != "cnn":
+        return "torch"                  # the native engine implements the reference CNN (any width)
     return "native" if device.type == "cuda" else "torch"
 
 
@@ -68,14 +70,15 @@ class Model:
     """Backend-dispatching model.  ``params`` / ``grads`` are flat arenas with the same plan."""
 
     def __init__(self, spec: ModelSpec, params: Arena, grads: Arena, cfg: Config,
-                 max_eval_batch: int = 2000):
+                 max_eval_batch: int = 2000, step_state: Optional[torch.Tensor] = None,
+                 worker: int = 0, num_workers: int = 1):
         self.spec, self.params, self.grads, self.cfg = spec, params, grads, cfg
         which = pick_backend(cfg, params.device)
         if which == "native":
             if params.device.type != "cuda":
                 raise RuntimeError("the native sm_100a backend needs a CUDA device; use --backend torch on CPU")
             from ..ops.engine import NativeBackend   # raises loudly if the .so is missing
-            self.impl = NativeBackend(spec, params, grads, cfg, max_eval_batch)
+            self.impl = NativeBackend(spec, params, grads, cfg, max_eval_batch, step_state, worker, num_workers)
         else:
             self.impl = TorchBackend(spec, params, grads, cfg)
         self.backend = self.impl.name

@@ -217,8 +217,13 @@ class HostWorker(_Common):
         if cfg.max_steps:
             nb = min(nb, cfg.max_steps)
         step = 0
+        steady_t0, steady_from = None, min(3, max(0, nb * cfg.epochs - 1))
         for epoch in range(cfg.epochs):
             for cnt in range(nb):
+                if step == steady_from:
+                    if self.device.type == "cuda":
+                        torch.cuda.synchronize()
+                    steady_t0 = time.perf_counter()
                 b, e = self.data.batch_slice(cnt, cfg.batch_size, self.windex, self.W, cfg.replicate_data)
                 with self.timers.phase("fwd_bwd"):
                     x = self.data.x_train[b:e].to(self.device, non_blocking=True)
@@ -235,13 +240,18 @@ class HostWorker(_Common):
                     M.log_eval(self.rank, epoch, cnt, acc)
                     self.sink.write(rank=self.rank, epoch=epoch, batch=cnt, accuracy=acc, loss=float(loss))
                 step += 1
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
+        steady_s = (time.perf_counter() - steady_t0) if steady_t0 is not None else float("nan")
         acc = self.model.accuracy(self.x_test, self.y_test)
         M.log_final(self.rank, acc)
         if cfg.log_time:
             M.log_time(time.process_time() - start_cpu)         # time.clock() parity (Q7)
         wall = time.perf_counter() - start_wall
         self.sink.write(rank=self.rank, final_accuracy=acc, wall_s=wall, phases=self.timers.summary(),
-                        samples_per_s=step * cfg.batch_size / max(wall, 1e-9))
+                        samples_per_s=step * cfg.batch_size / max(wall, 1e-9),
+                        steady_steps=step - steady_from, steady_s=steady_s,
+                        steady_samples_per_s=(step - steady_from) * cfg.batch_size / max(steady_s, 1e-9))
         if cfg.ckpt_path and self.rank == self.P:
             from ..utils.ckpt import save_checkpoint
             save_checkpoint(cfg.ckpt_path, self.params, step=step)

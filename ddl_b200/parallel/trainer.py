@@ -54,9 +54,9 @@ def init_group(device: torch.device, rank: int, world: int, timeout_s: float) ->
 def resolve_transport(cfg: Config, device: torch.device, world: int) -> str:
     t = cfg.transport
     if t == "auto":
-        if world == 1:
-            return "local"
-        return "fused" if device.type == "cuda" else "nccl"
+        if device.type == "cuda" and pick_backend(cfg, device) == "native":
+            return "fused"              # also for world == 1: the same K1 kernel, zero peers
+        return "local" if world == 1 else "nccl"
     if t == "fused" and device.type != "cuda":
         raise RuntimeError("the fused transport needs CUDA peer memory; use --transport nccl/host on CPU")
     if world == 1 and t in ("nccl", "fused") and device.type != "cuda":
@@ -84,7 +84,9 @@ class SPMDTrainer:
         self.sink = M.MetricsSink(cfg.metrics_path if rank == 0 or not cfg.metrics_path
                                   else cfg.metrics_path + ".%d" % rank)
         self.losses: List[float] = []
-        self.global_step = 0
+        self.global_step = getattr(self, "global_step", 0)
+        self._graph = None
+        self._graph_warmup = 2
 
     # ------------------------------------------------------------------------------
     def _build(self) -> None:
@@ -114,7 +116,8 @@ class SPMDTrainer:
             self.transport = self._T(cfg, lay, self.params, self.grads)
         if cfg.resume:
             self._load_opt_state(cfg.resume)
-        self.model = Model(self.spec, self.params, self.grads, cfg) if lay.is_worker else None
+        self.model = Model(self.spec, self.params, self.grads, cfg, step_state=getattr(self.transport, "st", None),
+                           worker=lay.my_worker or 0, num_workers=lay.num_workers) if lay.is_worker else None
         self.transport.initial_sync()
         if lay.is_worker:
             self.x_test = self.data.x_test.to(self.device)
@@ -142,8 +145,16 @@ class SPMDTrainer:
         return nb
 
     def train_step(self, cnt: int) -> Optional[torch.Tensor]:
+        """One training step through the public path: H2D of this step's batch from pinned host
+        memory, forward/backward, push + update + pull.  Returns the mean loss as a 0-d device
+        tensor (None on an owner-only rank)."""
         cfg, lay = self.cfg, self.layout
+        if self._graph is None and cfg.graphs and self._graphable and self.global_step >= self._graph_warmup:
+            self._capture()
+        if self._graph is not None:
+            return self._graph_step(cnt)
         loss = None
+        self.transport.begin_step()
         if lay.is_worker:
             b, e = self.data.batch_slice(cnt, cfg.batch_size, lay.my_worker, lay.num_workers,
                                          cfg.replicate_data)
@@ -156,6 +167,43 @@ class SPMDTrainer:
         self.global_step += 1
         return loss
 
+    # -- CUDA-graph fast path ------------------------------------------------------------
+    @property
+    def _graphable(self) -> bool:
+        return (self.device.type == "cuda" and self.transport.name == "fused"
+                and (self.model is None or self.model.backend == "native") and not self.cfg.profile)
+
+    def _capture(self) -> None:
+        """Capture [step-state advance, forward, backward, push+update+pull] once; every later step
+        is one H2D copy pair + one graph launch (phases are 10-100 us, launch
+        latency would dominate otherwise)."""
+        cfg, lay = self.cfg, self.layout
+        if lay.is_worker:
+            self._x_static = torch.zeros(cfg.batch_size, 784, device=self.device)
+            self._y_static = torch.zeros(cfg.batch_size, dtype=torch.int32, device=self.device)
+        torch.cuda.synchronize()
+        from ..ops import native
+        l0 = native.LAUNCHES
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.transport.begin_step()
+            if lay.is_worker:
+                self.model.impl.enqueue_train_step(self._x_static, self._y_static)
+            self.transport.step()
+        self._graph = g
+        self.launches_per_step = native.LAUNCHES - l0      # kernels of ours inside one replay
+        # the capture itself did not execute anything; global_step is untouched
+
+    def _graph_step(self, cnt: int) -> Optional[torch.Tensor]:
+        cfg, lay = self.cfg, self.layout
+        if lay.is_worker:
+            b, e = self.data.batch_slice(cnt, cfg.batch_size, lay.my_worker, lay.num_workers, cfg.replicate_data)
+            self._x_static.copy_(self.data.x_train[b:e], non_blocking=True)
+            self._y_static.copy_(self.data.y_train[b:e], non_blocking=True)
+        self._graph.replay()
+        self.global_step += 1
+        return self.transport.loss(cfg.batch_size) if lay.is_worker else None
+
     def evaluate(self) -> float:
         return self.model.accuracy(self.x_test, self.y_test)
 
@@ -166,7 +214,10 @@ class SPMDTrainer:
         lrank = None if lay.kind == "single" and os.environ.get("DDL_ROLE", "") == "single" \
             else lay.logical_worker_rank
         acc = float("nan")
-        for epoch in range(cfg.epochs):
+        serve_only = (not lay.is_worker) and cfg.mode == "async" and self.transport.name == "fused"
+        if serve_only:
+            self.transport.serve_async()
+        for epoch in range(cfg.epochs if not serve_only else 0):
             for cnt in range(nb):
                 loss = self.train_step(cnt)
                 if lay.is_worker:
@@ -177,6 +228,8 @@ class SPMDTrainer:
                         self.losses.append(float(loss))
                         self.sink.write(rank=lay.rank, epoch=epoch, batch=cnt, accuracy=acc,
                                         loss=self.losses[-1])
+        if hasattr(self.transport, "finish"):
+            self.transport.finish()
         if self.device.type == "cuda":
             torch.cuda.synchronize()
         wall = time.perf_counter() - start_wall

@@ -44,6 +44,9 @@ class SpmdTransport:
     def initial_sync(self) -> None:
         raise NotImplementedError
 
+    def begin_step(self) -> None:
+        """Called before the worker's forward/backward of each step (device step-state advance)."""
+
     def step(self) -> None:
         """push + update + pull for one training step (sync) or one async round."""
         raise NotImplementedError

@@ -1,0 +1,314 @@
+"""``fused`` transport: the product.  Push, gradient reduction, optimizer and pull are sm_100a kernels
+that read and write the peers' arenas directly over NVLink / NVSwitch (csrc/comm.cu).
+
+What it replaces in the reference (per step and per worker): 14 blocking ``comm.Send`` + 14
+``comm.Recv`` of host numpy buffers (mnist_sync_sharding/worker.py:36,94), the PS-side Python loop
+with ``numpy +=`` and a ``Session.run`` of ApplyAdam (mnist_sync_sharding/parameter_server.py:76-82,
+112-126) and 14 ``tf.assign`` feeds (worker.py:97).  Here:
+
+* every rank allocates its gradient arena, parameter arena, (async) accumulator and a 256-byte
+  signal pad with the library's own allocator and publishes cudaIpc handles; every rank maps all of
+  them once (``SymmetricMemory``) - the "symmetric, peer-mapped memory" of SURVEY 5.8;
+* sync step  = ONE kernel per rank: barrier -> owner reduces its range from all workers' gradient
+  arenas in fixed order -> scale -> SGD / momentum / TF1-Adam in place -> stores the new values into
+  every worker's parameter arena -> barrier (K1 + K3);
+* async step = remote ``red.global.add.v4.f32`` of the gradient into the owners' accumulators with a
+  release-ordered push counter (K2), owner-side exactly-once consumption + optimizer + version bump,
+  and a barrier-free pull (K3).  Staleness (owner version at push - version at last pull) is
+  histogrammed on the device.
+
+All per-step scalars (step count, Adam step size, dropout stream, barrier epochs) live in a
+device-resident ``DdlStepState`` so a whole step replays from a CUDA graph.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ...config import Config
+from ...models.spec import ModelSpec
+from ...optim import FlatOptimizer
+from ...ops import native
+from ..arena import Arena
+from ..roles import RankLayout
+from ..sharding import ShardPlan
+from .collective import SpmdTransport
+
+_KIND = {"sgd": 0, "momentum": 1, "adam": 2}
+
+
+class _RawCuda:
+    """Zero-copy torch view of library-allocated device memory (``__cuda_array_interface__``)."""
+
+    def __init__(self, ptr: int, n: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def _as_tensor(ptr: int, n: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+    ts = {torch.float32: "<f4", torch.int32: "<i4"}[dtype]
+    return torch.as_tensor(_RawCuda(ptr, n, ts), device=device)
+
+
+class SymmetricMemory:
+    """One buffer per rank, same size everywhere, every rank holds a device pointer to every copy."""
+
+    def __init__(self, nbytes: int, rank: int, world: int, device: torch.device):
+        self.L = native.lib()
+        self.rank, self.world, self.nbytes, self.device = rank, world, nbytes, device
+        p = C.c_void_p()
+        native.check(self.L.ddl_dev_malloc(C.byref(p), nbytes), "ddl_dev_malloc")
+        self.local = p.value
+        self.ptrs: List[int] = [0] * world
+        self.ptrs[rank] = self.local
+        self.opened: List[int] = []
+        if world > 1:
+            h = C.create_string_buffer(64)
+            native.check(self.L.ddl_ipc_export(self.local, h), "ddl_ipc_export")
+            handles: List[Optional[bytes]] = [None] * world
+            dist.all_gather_object(handles, h.raw)
+            for r in range(world):
+                if r == rank:
+                    continue
+                q = C.c_void_p()
+                native.check(self.L.ddl_ipc_open(handles[r], C.byref(q)), "ddl_ipc_open(rank %d)" % r)
+                self.ptrs[r] = q.value
+                self.opened.append(q.value)
+
+    def tensor(self, dtype=torch.float32) -> torch.Tensor:
+        return _as_tensor(self.local, self.nbytes // 4, dtype, self.device)
+
+    def close(self) -> None:
+        for q in self.opened:
+            self.L.ddl_ipc_close(q)
+        self.opened = []
+        if self.local:
+            self.L.ddl_dev_free(self.local)
+            self.local = 0
+
+
+class FusedTransport(SpmdTransport):
+    name = "fused"
+
+    @classmethod
+    def create(cls, cfg: Config, layout: RankLayout, spec: ModelSpec, plan: ShardPlan,
+               device: torch.device) -> "FusedTransport":
+        L = native.lib()
+        native.check(L.ddl_set_device(device.index or 0), "ddl_set_device")
+        world = layout.world
+        if world > native.MAX_PEERS:
+            raise native.NativeError("fused transport supports at most %d ranks" % native.MAX_PEERS)
+        if world > 1:
+            for r in range(torch.cuda.device_count()):
+                if r != (device.index or 0) and r < world and not L.ddl_can_access_peer(device.index or 0, r):
+                    raise native.NativeError("GPU %d cannot access GPU %d: no NVLink/P2P path" % (device.index or 0, r))
+        nbytes = plan.total * 4
+        mem = {"params": SymmetricMemory(nbytes, layout.rank, world, device),
+               "grads": SymmetricMemory(nbytes, layout.rank, world, device),
+               "pad": SymmetricMemory(native.PAD_SLOTS * 4, layout.rank, world, device)}
+        if cfg.mode == "async":
+            mem["accum"] = SymmetricMemory(nbytes, layout.rank, world, device)
+        params = Arena(spec, plan, device, mem["params"].tensor())
+        grads = Arena(spec, plan, device, mem["grads"].tensor())
+        return cls(cfg, layout, params, grads, mem)
+
+    def __init__(self, cfg, layout, params, grads, mem: Dict[str, SymmetricMemory]):
+        super().__init__(cfg, layout, params, grads)
+        self.L = native.lib()
+        self.mem = mem
+        dev = params.device
+        lay = layout
+        self.kind = _KIND[cfg.optimizer]
+        # optimizer state for my ranges, indexed like the arena (only owned ranges are touched)
+        owns = bool(lay.my_shards)
+        self.m = torch.zeros(self.plan.total, device=dev) if owns and self.kind >= 1 else None
+        self.v = torch.zeros(self.plan.total, device=dev) if owns and self.kind == 2 else None
+        seed = 0 if cfg.seed is None else cfg.seed
+        self.st = native.new_step_state(seed, lay.my_worker or 0, lay.num_workers)
+        self.scratch = torch.zeros(64, dtype=torch.int32, device=dev)      # done counters, applied/pending ...
+        self.pulled_version = torch.zeros(native.MAX_PEERS, dtype=torch.int32, device=dev)
+        self.stale_hist = torch.zeros(native.STALE_BINS, dtype=torch.int32, device=dev)
+        self.comm = native.Comm()
+        self.comm.rank, self.comm.world = lay.rank, lay.world
+        for r in range(lay.world):
+            self.comm.grads[r] = mem["grads"].ptrs[r]
+            self.comm.params[r] = mem["params"].ptrs[r]
+            self.comm.pads[r] = mem["pad"].ptrs[r]
+            self.comm.accum[r] = mem["accum"].ptrs[r] if "accum" in mem else None
+        self.worker_mask = 0
+        for wr in lay.worker_ranks:
+            self.worker_mask |= 1 << wr
+        # per-owned-shard argument blocks
+        self.sync_args: List[native.SyncArgs] = []
+        for r in lay.my_shards:
+            a = native.SyncArgs()
+            a.begin, a.end = self.plan.shard_range[r]
+            a.m = self.m.data_ptr() if self.m is not None else None
+            a.v = self.v.data_ptr() if self.v is not None else None
+            a.st = self.st.data_ptr()
+            a.done_counter = self.scratch.data_ptr()
+            a.worker_mask = self.worker_mask
+            a.dest_mask = self.worker_mask
+            kind, step, aa, bb, eps = FlatOptimizer(torch.zeros(1), cfg.optimizer, cfg.lr, cfg.beta1, cfg.beta2,
+                                                    cfg.eps, cfg.momentum, use_native=False).hyper(1)
+            a.lr, a.a, a.b, a.eps = cfg.lr, aa, bb, eps
+            a.gscale = self.gscale if cfg.mode == "sync" else 1.0
+            for k in range(native.MAX_SKIP):
+                a.skip_begin[k] = a.skip_end[k] = -1
+            self.sync_args.append(a)
+        if not self.sync_args:                       # worker-only rank: still takes part in the barriers
+            a = native.SyncArgs()
+            a.begin = a.end = 0
+            a.st = self.st.data_ptr()
+            a.done_counter = self.scratch.data_ptr()
+            a.worker_mask = a.dest_mask = self.worker_mask
+            for k in range(native.MAX_SKIP):
+                a.skip_begin[k] = a.skip_end[k] = -1
+            self.sync_args.append(a)
+        self.async_args = native.AsyncArgs()
+        aa = self.async_args
+        aa.num_shards = lay.num_ps
+        for r in range(lay.num_ps):
+            aa.owner_rank[r] = lay.owner_rank(r)
+            aa.shard_begin[r], aa.shard_end[r] = self.plan.shard_range[r]
+        aa.direct_sgd = 1 if (cfg.mode == "async" and cfg.optimizer == "sgd") else 0
+        aa.lr = cfg.lr
+        aa.done_counter = self.scratch[1:].data_ptr()
+        aa.pulled_version = self.pulled_version.data_ptr()
+        aa.stale_hist = self.stale_hist.data_ptr()
+        self.barrier_epoch = self.scratch[8:]
+
+    # ------------------------------------------------------------------------------
+    def _s(self) -> int:
+        return native.stream_ptr()
+
+    def barrier(self) -> None:
+        """Host-requested device-side barrier across all ranks (one tiny kernel per rank)."""
+        if self.layout.world > 1:
+            native.check(self.L.ddl_device_barrier(C.byref(self.comm), self.barrier_epoch.data_ptr(), self._s()),
+                         "ddl_device_barrier")
+            native.count()
+
+    def pull_all(self) -> None:
+        native.check(self.L.ddl_pull_allgather(C.byref(self.comm), C.byref(self.async_args), self._s()),
+                     "ddl_pull_allgather")
+        native.count()
+
+    def initial_sync(self) -> None:
+        """Initial pull (Q5): every rank copies each owner's range; owners are the source of truth."""
+        if self.layout.world > 1:
+            torch.cuda.synchronize()
+            dist.barrier()
+            self.pull_all()
+            torch.cuda.synchronize()
+            dist.barrier()
+
+    def begin_step(self) -> None:
+        c = self.cfg
+        native.check(self.L.ddl_step_advance(self.st.data_ptr(), c.lr, c.beta1, c.beta2,
+                                             1 if c.mode == "sync" else 0, self._s()), "ddl_step_advance")
+        native.count()
+
+    def step(self) -> None:
+        if self.cfg.mode == "sync":
+            for a in self.sync_args:
+                native.check(self.L.ddl_sync_push_update_pull(C.byref(self.comm), C.byref(a), self.kind, self._s()),
+                             "ddl_sync_push_update_pull")
+                native.count()
+        else:
+            if self.layout.is_worker:
+                native.check(self.L.ddl_async_push(C.byref(self.comm), C.byref(self.async_args), self._s()),
+                             "ddl_async_push")
+                native.count()
+            self.apply_pending()
+            if self.layout.is_worker:
+                self.pull_all()
+        self.step_count += 1
+
+    def apply_pending(self) -> None:
+        """Owner side of async mode: consume whatever has been pushed since the last call."""
+        if self.async_args.direct_sgd or not self.layout.my_shards:
+            return
+        c = self.cfg
+        for a in self.sync_args:
+            native.check(self.L.ddl_async_apply(C.byref(self.comm), C.byref(a), self.kind,
+                                                self.scratch[2:].data_ptr(), self.scratch[3:].data_ptr(),
+                                                c.beta1, c.beta2, self._s()), "ddl_async_apply")
+            native.count(2)
+
+    def serve_async(self, poll_every: int = 8) -> int:
+        """Dedicated async PS rank (mnist_async/parameter_server.py:52-69 without the host loop body):
+        keep consuming pushes until every worker has announced completion through the store."""
+        store = dist.distributed_c10d._get_default_store()
+        keys = ["ddl_done_%d" % wr for wr in self.layout.worker_ranks]
+        rounds = 0
+        while True:
+            for _ in range(poll_every):
+                self.apply_pending()
+                rounds += 1
+            torch.cuda.current_stream().synchronize()
+            if store.check(keys):
+                break
+        return rounds
+
+    def finish(self) -> None:
+        """End of an async run: drain every accumulator and give all workers the final weights."""
+        if self.cfg.mode != "async" or self.layout.world == 1:
+            if self.cfg.mode == "async":
+                self.apply_pending()
+            return
+        if self.layout.is_worker:
+            torch.cuda.synchronize()
+            dist.distributed_c10d._get_default_store().set("ddl_done_%d" % self.layout.rank, "1")
+        torch.cuda.synchronize()
+        dist.barrier()                       # all pushes have landed
+        self.apply_pending()
+        torch.cuda.synchronize()
+        dist.barrier()                       # all owners have applied
+        if self.layout.is_worker:
+            self.pull_all()
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------------------
+    def loss(self, batch: int) -> torch.Tensor:
+        return self.st.view(torch.float32)[2] / batch
+
+    def stats(self) -> Dict[str, object]:
+        s = native.read_step_state(self.st)
+        out = {"optimizer_steps": s["t"], "worker_steps": s["wstep"]}
+        if self.cfg.mode == "async":
+            out["staleness_hist"] = self.stale_hist.cpu().tolist()
+            pad = self.mem["pad"].tensor(torch.int32).cpu()
+            out["pushes_received"] = int(pad[native.PAD_PUSHES])
+            out["shard_version"] = int(pad[native.PAD_VERSION])
+        return out
+
+    def opt_state(self):
+        lay = self.layout
+        m = self.m if self.m is not None else torch.zeros_like(self.params.flat)
+        v = self.v if self.v is not None else torch.zeros_like(self.params.flat)
+        t = torch.tensor([native.read_step_state(self.st)["t"]], device=self.params.device)
+        if lay.world > 1:
+            m, v = m.clone(), v.clone()
+            for r in range(lay.num_ps):
+                dist.broadcast(self.params.shard(r, m), src=lay.owner_rank(r))
+                dist.broadcast(self.params.shard(r, v), src=lay.owner_rank(r))
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return {"m": m, "v": v, "t": int(t.item())}
+
+    def load_opt_state(self, m, v, t) -> None:
+        if self.m is not None and m is not None and m is not self.m:
+            self.m.copy_(m)
+        if self.v is not None and v is not None and v is not self.v:
+            self.v.copy_(v)
+        self.st[0] = int(t)
+
+    def close(self) -> None:
+        torch.cuda.synchronize()
+        if self.layout.world > 1 and dist.is_initialized():
+            dist.barrier()
+        for mem in self.mem.values():
+            mem.close()
+        self.mem = {}

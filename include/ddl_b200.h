@@ -1,0 +1,180 @@
+/* ddl_b200 native library - C ABI.
+ *
+ * Every entry point returns 0 on success and a negative code on failure; ddl_last_error()
+ * then holds a human-readable message.  Pointers are device pointers unless noted.  All work
+ * is enqueued on the given stream; nothing synchronises unless documented.
+ *
+ * The reference (epikjjh/DIstributed-Deep-Learning) contains no native code: each entry point
+ * cites the TensorFlow / mpi4py call site whose work it takes over.
+ */
+#ifndef DDL_B200_H_
+#define DDL_B200_H_
+
+#include <stdint.h>
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDL_MAX_PEERS 16
+
+/* Device-resident per-step scalars (one 64-byte line).  Kept on the device so a whole training
+ * step can be replayed from a CUDA graph with no host-written kernel arguments. */
+typedef struct DdlStepState {
+  uint32_t t;             /* optimizer steps applied to my shard (sync: == worker steps)        */
+  float lr_t;             /* TF1 Adam step size for step t                                      */
+  float loss_sum;         /* sum of per-sample cross-entropy of the current batch               */
+  uint32_t correct;       /* correctly classified samples of the current batch                  */
+  uint32_t seed;          /* dropout seed                                                       */
+  uint32_t stream;        /* dropout stream of this step's first dropout layer (+1 for the next) */
+  uint32_t wstep;         /* worker steps started                                                */
+  uint32_t stream_base;   /* 2 * worker index                                                    */
+  uint32_t stream_stride; /* 2 * number of workers: stream = base + (wstep-1) * stride           */
+  uint32_t pad[7];
+} DdlStepState;
+
+const char* ddl_last_error(void);
+int ddl_version(void);
+int ddl_memcpy_async(void* dst, const void* src, size_t bytes, cudaStream_t s);
+
+/* ---- step state / optimizers (ApplyAdam: mnist_sync/parameter_server.py:21-27; model.py:106) */
+/* Start of a worker step: wstep += 1, dropout stream, loss/correct reset; when advance_opt != 0
+ * also t += 1 and lr_t (sync mode, where the shard steps in lock-step with the workers). */
+int ddl_step_advance(DdlStepState* st, float lr, float b1, float b2, int advance_opt, cudaStream_t s);
+/* kind 0 sgd | 1 momentum | 2 adam(TF1).  p, m, v, g are 16B-aligned ranges of n floats.
+ * step_size is lr (sgd, momentum) or lr_t (adam; read from st->lr_t when st != NULL).
+ * a = momentum or beta1, b = beta2.  g is multiplied by gscale first (sum/mean choice, Q3). */
+int ddl_optimizer_step(int kind, float* p, float* m, float* v, const float* g, int64_t n,
+                       float step_size, float a, float b, float eps, float gscale,
+                       const DdlStepState* st, cudaStream_t s);
+
+/* ---- SIMT model ops ------------------------------------------------------------------------ */
+/* conv1 (Cin=1) + bias + ReLU + 2x2 SAME max-pool (model.py:24-31).  idx may be NULL (eval). */
+int ddl_conv1_relu_pool(const float* x, const float* w, const float* bias, float* y, uint8_t* idx,
+                        int B, int S, int C, cudaStream_t s);
+int ddl_conv1_wgrad(const float* x, const float* dy, float* dw, float* db, int B, int S, int C,
+                    cudaStream_t s);
+/* (bias +) ReLU + tf.nn.max_pool2d 2x2/2 SAME on NHWC conv sums and its gradient (model.py:31,42,53,64);
+ * the backward also accumulates the bias gradient of the producing conv into db (may be NULL). */
+int ddl_maxpool_fwd(const float* a, const float* bias, float* y, uint8_t* idx, int B, int H, int W, int C,
+                    cudaStream_t s);
+int ddl_maxpool_bwd(const float* dp, const uint8_t* idx, float* dy, float* db, int B, int H, int W, int C,
+                    cudaStream_t s);
+int ddl_colsum(const float* x, float* out, int R, int C, cudaStream_t s);
+/* fc3 + softmax_cross_entropy_with_logits + reduce_mean (model.py:85-92) and accuracy
+ * (model.py:104-105).  dlogits = (softmax - onehot) * scale.  logits / dlogits / labels may be NULL. */
+int ddl_fc3_xent_fwd(const float* h, const float* w, const float* bias, const int* labels, float* logits,
+                     float* dlogits, DdlStepState* st, int B, int K, int NC, float scale, cudaStream_t s);
+int ddl_fc3_bwd(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, int B, int K,
+                int NC, uint32_t seed, uint32_t stream, float keep_prob, cudaStream_t s);
+/* same, dropout seed/stream read from the device step state (graph-replay safe) */
+int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, int B, int K,
+                   int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob, cudaStream_t s);
+int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int B, int NC, cudaStream_t s);
+
+/* ---- tcgen05 implicit-GEMM plans (csrc/tc_gemm.cu) ------------------------------------------
+ * conv2..4 forward (tf.nn.conv2d, model.py:39,50,61), their backprop-input / backprop-filter,
+ * and the fc1 / fc2 matmuls forward and backward (model.py:70,79).  A plan owns the TMA
+ * descriptors for fixed pointers/shapes; running it is one kernel launch.
+ *   act plan, dgrad=0: out[pix,n] = epi(sum_{tap,c} act[pix+off(tap), c] * w[tap][c][n])   (w: HWIO)
+ *   act plan, dgrad=1: out[pix,n] = epi(sum_{tap,c} act[pix-off(tap), c] * w[tap][n][c])
+ *   wgrad plan:        out[tap][b][a] += sum_pix g[pix,a] * x[pix+off(tap), b]
+ * flags: 1 bias, 2 relu, 4 dropout (seed/stream from st), 8 multiply by (mask_act > 0) * mask_scale.
+ * ksplit > 1 accumulates raw sums with red.add into a pre-zeroed out (no bias/relu/dropout). */
+typedef struct DdlTcPlan DdlTcPlan;
+DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
+                           int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
+                           const float* mask_act, float mask_scale, const DdlStepState* st,
+                           uint32_t drop_stream_off, float keep_prob);
+DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,
+                             int ksize, int ntile, int psplit);
+int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);
+void ddl_tc_plan_destroy(DdlTcPlan* pl);
+int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8);
+
+/* ---- peer-memory communication (csrc/comm.cu) -----------------------------------------------
+ * Replaces the reference's mpi4py layer (SURVEY 2.3 call-site table). */
+#define DDL_MAX_SKIP 4
+#define DDL_STALE_BINS 16
+/* signal pad layout (uint32 slots, one pad per rank) */
+#define DDL_PAD_BARRIER 16   /* [16,32): host-requested device barrier epochs, one slot per source */
+#define DDL_PAD_PUSHES 32    /* async: complete pushes landed in this owner's accumulator          */
+#define DDL_PAD_VERSION 33   /* async: optimizer applications done by this owner                   */
+#define DDL_PAD_SLOTS 64
+
+typedef struct DdlComm {
+  int rank, world;
+  float* grads[DDL_MAX_PEERS];     /* every rank's gradient arena (peer-mapped)   */
+  float* params[DDL_MAX_PEERS];    /* every rank's parameter arena                */
+  float* accum[DDL_MAX_PEERS];     /* every rank's async gradient accumulator     */
+  uint32_t* pads[DDL_MAX_PEERS];   /* every rank's signal pad                     */
+} DdlComm;
+
+typedef struct DdlSyncArgs {
+  int64_t begin, end;              /* my owned arena range (elements, multiples of 4) */
+  float* m; float* v;              /* optimizer state, indexed like the arena          */
+  DdlStepState* st;
+  uint32_t* done_counter;          /* device scratch word, zero between launches        */
+  uint32_t worker_mask;            /* ranks whose gradients are summed                  */
+  uint32_t dest_mask;              /* ranks that receive the updated range              */
+  float lr, a, b, eps, gscale;
+  int64_t skip_begin[DDL_MAX_SKIP], skip_end[DDL_MAX_SKIP];   /* not broadcast (K4 pulls them) */
+} DdlSyncArgs;
+
+typedef struct DdlAsyncArgs {
+  int num_shards;
+  int owner_rank[DDL_MAX_PEERS];
+  int64_t shard_begin[DDL_MAX_PEERS], shard_end[DDL_MAX_PEERS];
+  int direct_sgd;                  /* 1: red.add(-lr*g) straight into the owners' parameters */
+  float lr;
+  uint32_t* done_counter;
+  uint32_t* pulled_version;        /* [num_shards] owner version seen at the last pull    */
+  uint32_t* stale_hist;            /* [DDL_STALE_BINS] staleness histogram of my pushes   */
+} DdlAsyncArgs;
+
+int ddl_dev_malloc(void** p, size_t bytes);
+int ddl_dev_free(void* p);
+int ddl_ipc_export(void* p, void* handle64);
+int ddl_ipc_open(const void* handle64, void** p);
+int ddl_ipc_close(void* p);
+int ddl_set_device(int dev);
+int ddl_can_access_peer(int dev, int peer);
+/* K1 + K3, sync mode (SS/worker.py:36 + SS/ps.py:112-126 + SS/worker.py:90-97). */
+int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, cudaStream_t s);
+/* K2, async mode (AS/worker.py:36 + AS/ps.py:99-111). */
+int ddl_async_push(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s);
+int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, uint32_t* applied, uint32_t* pending,
+                    float b1, float b2, cudaStream_t s);
+/* K3 stand-alone (initial pull, async pull, pre-eval refresh). */
+int ddl_pull_allgather(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s);
+int ddl_device_barrier(const DdlComm* c, uint32_t* epoch_counter, cudaStream_t s);
+
+/* ---- native step executor (csrc/engine.cu) ---------------------------------------------------
+ * The TF1 graph + Session of model.py:17-112 as enqueue-only C calls (CUDA-graph capturable). */
+typedef struct DdlEngineCfg {
+  int kind;                 /* 0 cnn (the reference model, optionally widened) */
+  int width_mult;
+  int batch;                /* training batch size (reference: 100)            */
+  int max_eval_batch;       /* largest evaluation chunk                         */
+  float keep_prob;
+  float* params;            /* flat parameter arena                             */
+  float* grads;             /* flat gradient arena                              */
+  int64_t arena_elems;
+  int64_t var_offset[16];   /* element offset of v0..v13 in both arenas          */
+  DdlStepState* st;
+} DdlEngineCfg;
+typedef struct DdlEngine DdlEngine;
+DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg);
+void ddl_engine_destroy(DdlEngine* e);
+/* sess.run(self.grads, keep_prob=.5) (mnist_sync/worker.py:30): x [B,784], y [B] class ids */
+int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream_t s);
+/* sess.run(self.accuracy, keep_prob=1) (mnist_sync/worker.py:72) over n rows */
+int ddl_engine_eval(DdlEngine* e, const float* x, const int* y, int n, unsigned* correct, float* logits_out,
+                    cudaStream_t s);
+const float* ddl_engine_buffer(const DdlEngine* e, int which);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDL_B200_H_ */

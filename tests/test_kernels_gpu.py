@@ -1,0 +1,254 @@
+"""Unit tier, GPU: every sm_100a kernel against a plain PyTorch fp32 reference of the same op
+(SURVEY 4).  Shapes are the reference model's, including the awkward ones: B=100 (not tile
+aligned), 7x7 -> 4x4 SAME pool, N=10 logits."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+TF32_TOL = 4e-3     # tf32 multiply (10-bit mantissa, truncated inputs), fp32 accumulate
+
+
+def dev():
+    return torch.device("cuda")
+
+
+def rel_err(a, b):
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+def to_ref(t):
+    """fp32 reference math must not itself run in tf32."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return t
+
+
+def ref_conv(x_nhwc, w_hwio):
+    to_ref(None)
+    return F.conv2d(x_nhwc.permute(0, 3, 1, 2).double(), w_hwio.permute(3, 2, 0, 1).double(), padding=2) \
+        .permute(0, 2, 3, 1).float()
+
+
+def test_native_library_loaded_and_blackwell():
+    from ddl_b200.ops import native
+    assert native.lib().ddl_version() == 100
+    assert torch.cuda.get_device_capability()[0] == 10, "these kernels are sm_100a only"
+
+
+@pytest.mark.parametrize("kind", ["adam", "sgd", "momentum"])
+def test_optimizer_kernels_match_oracle(kind):
+    from ddl_b200.models.oracle import OracleOptimizer
+    from ddl_b200.optim import FlatOptimizer
+    torch.manual_seed(0)
+    n = 100_003 * 4 // 4 * 4 + 64
+    p0 = torch.randn(n)
+    ref_p, ref = p0.clone(), OracleOptimizer(p0, kind, 1e-3)
+    p = p0.to(dev())
+    opt = FlatOptimizer(p, kind, 1e-3)
+    for s in range(3):
+        g = torch.randn(n)
+        ref.step(ref_p, g * 0.5)
+        opt.step(p, g.to(dev()), 0.5)
+    assert torch.allclose(p.cpu(), ref_p, atol=1e-6, rtol=1e-5)
+
+
+def test_conv1_relu_pool_and_wgrad():
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(1)
+    B, C = 100, 32
+    x = torch.rand(B, 28, 28, device=dev())
+    w = (torch.randn(5, 5, 1, C, device=dev()) * 0.2).requires_grad_(True)
+    b = (torch.randn(C, device=dev()) * 0.1).requires_grad_(True)
+    to_ref(None)
+    a = F.relu(F.conv2d(x[:, None], w.permute(3, 2, 0, 1), b, padding=2))
+    ref = F.max_pool2d(a, 2, 2).permute(0, 2, 3, 1)
+    y, idx = K.conv1_relu_pool(x, w.detach(), b.detach())
+    assert rel_err(y, ref.detach()) < 1e-5
+    # backward: route a pooled gradient, then wgrad
+    dp = torch.randn_like(ref)
+    ref.backward(dp)
+    dy, _ = K.maxpool_relu_bwd(dp.contiguous(), idx, 28, 28, want_db=False)
+    dw, db = K.conv1_wgrad(x, dy)
+    assert rel_err(dw, w.grad) < 1e-4 and rel_err(db, b.grad) < 1e-4
+
+
+@pytest.mark.parametrize("H,C", [(14, 64), (7, 128), (4, 256)])
+def test_bias_relu_maxpool_fwd_bwd(H, C):
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(2)
+    B = 100
+    a = torch.randn(B, H, H, C, device=dev(), requires_grad=True)
+    bias = torch.randn(C, device=dev(), requires_grad=True)
+    ref = F.max_pool2d(F.relu(a + bias).permute(0, 3, 1, 2), 2, 2, ceil_mode=True).permute(0, 2, 3, 1)
+    y, idx = K.bias_relu_maxpool(a.detach(), bias.detach())
+    assert y.shape == ref.shape and torch.allclose(y, ref.detach(), atol=1e-6)
+    dp = torch.randn_like(ref)
+    ref.backward(dp)
+    dy, db = K.maxpool_relu_bwd(dp.contiguous(), idx, H, H)
+    assert torch.allclose(dy, a.grad, atol=1e-6)
+    assert rel_err(db, bias.grad) < 1e-4
+
+
+@pytest.mark.parametrize("H,Cin,Cout,B", [(14, 32, 64, 100), (7, 64, 128, 100), (4, 128, 256, 100), (14, 32, 64, 37)])
+def test_tc_conv_fprop(H, Cin, Cout, B):
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(3)
+    x = torch.randn(B, H, H, Cin, device=dev())
+    w = torch.randn(5, 5, Cin, Cout, device=dev()) * 0.05
+    ref = ref_conv(x, w)
+    out = K.conv5x5_fprop(x, w)
+    assert rel_err(out, ref) < TF32_TOL
+    out32 = K.conv5x5_fprop(x, w, ntile=32)
+    assert rel_err(out32, ref) < TF32_TOL
+    outs = K.conv5x5_fprop(x, w, ntile=32, ksplit=3)
+    assert rel_err(outs, ref) < TF32_TOL
+
+
+@pytest.mark.parametrize("H,Cin,Cout", [(14, 32, 64), (7, 64, 128), (4, 128, 256)])
+def test_tc_conv_dgrad_wgrad(H, Cin, Cout):
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(4)
+    B = 100
+    x = torch.randn(B, H, H, Cin, device=dev(), dtype=torch.float64, requires_grad=True)
+    w = (torch.randn(5, 5, Cin, Cout, device=dev(), dtype=torch.float64) * 0.05).requires_grad_(True)
+    y = F.conv2d(x.permute(0, 3, 1, 2), w.permute(3, 2, 0, 1), padding=2).permute(0, 2, 3, 1)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    dyf, xf, wf = dy.float().contiguous(), x.detach().float().contiguous(), w.detach().float().contiguous()
+    dx = K.conv5x5_dgrad(dyf, wf)
+    assert rel_err(dx, x.grad.float()) < TF32_TOL
+    dx2 = K.conv5x5_dgrad(dyf, wf, ntile=32, ksplit=2)
+    assert rel_err(dx2, x.grad.float()) < TF32_TOL
+    dw = K.conv5x5_wgrad(dyf, xf)
+    assert rel_err(dw, w.grad.float()) < TF32_TOL
+    dw2 = K.conv5x5_wgrad(dyf, xf, psplit=5)
+    assert rel_err(dw2, w.grad.float()) < TF32_TOL
+
+
+@pytest.mark.parametrize("B,Kin,N", [(100, 1024, 1024), (100, 1024, 512), (8, 1024, 512), (128, 64, 32)])
+def test_tc_linear_fwd_dx_dw(B, Kin, N):
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(5)
+    x = torch.randn(B, Kin, device=dev())
+    w = torch.randn(Kin, N, device=dev()) * 0.05
+    b = torch.randn(N, device=dev())
+    ref = x.double() @ w.double() + b.double()
+    out = K.linear_fwd(x, w, b)
+    assert rel_err(out, ref.float()) < TF32_TOL
+    out = K.linear_fwd(x, w, b, relu=True)
+    assert rel_err(out, ref.float().relu()) < TF32_TOL
+    dy = torch.randn(B, N, device=dev())
+    dx = K.linear_dx(dy, w)
+    assert rel_err(dx, (dy.double() @ w.double().t()).float()) < TF32_TOL
+    act = torch.randn(B, Kin, device=dev())
+    dxm = K.linear_dx(dy, w, act, 2.0)
+    assert rel_err(dxm, ((dy.double() @ w.double().t()) * (act > 0) * 2.0).float()) < TF32_TOL
+    dw = K.linear_dw(dy, x)
+    assert rel_err(dw, (x.double().t() @ dy.double()).float()) < TF32_TOL
+
+
+def test_tc_linear_dropout_matches_oracle_hash():
+    from ddl_b200.models.oracle import dropout_keep_mask
+    from ddl_b200.ops import functional as K, native
+    torch.manual_seed(6)
+    B, Kin, N = 100, 1024, 512
+    x = torch.randn(B, Kin, device=dev())
+    w = torch.randn(Kin, N, device=dev()) * 0.05
+    b = torch.randn(N, device=dev())
+    st = native.new_step_state(seed=11)
+    st[5] = 6                                   # stream of this step
+    out = K.linear_fwd(x, w, b, dropout=(st, 1, 0.5))
+    mask = dropout_keep_mask(11, 7, B * N, 0.5, dev()).view(B, N)
+    ref = (x.double() @ w.double() + b.double()).float() * mask / 0.5
+    assert torch.equal(out == 0, ~mask | (ref == 0))
+    assert rel_err(out, ref) < TF32_TOL
+
+
+def test_fc3_softmax_xent_and_backward():
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(7)
+    B, Kin, NC = 100, 512, 10
+    h = torch.randn(B, Kin, device=dev(), requires_grad=True)
+    w = (torch.randn(Kin, NC, device=dev()) * 0.1).requires_grad_(True)
+    b = torch.randn(NC, device=dev(), requires_grad=True)
+    y = torch.randint(0, NC, (B,), device=dev(), dtype=torch.int32)
+    logits_ref = h @ w + b
+    loss = F.cross_entropy(logits_ref, y.long())
+    loss.backward()
+    logits, dl, loss_sum, correct = K.fc3_softmax_xent(h.detach(), w.detach(), b.detach(), y)
+    assert torch.allclose(logits, logits_ref.detach(), atol=1e-4)
+    assert abs(loss_sum / B - float(loss)) < 1e-4
+    assert correct == int((logits_ref.argmax(1) == y.long()).sum())
+    dw, db, dh = K.fc3_bwd(h.detach(), w.detach(), dl)
+    assert rel_err(dw, w.grad) < 1e-4 and rel_err(db, b.grad) < 1e-4 and rel_err(dh, h.grad) < 1e-4
+
+
+def _engine_setup(batch=100, keep_prob=0.5, seed=5, wm=1):
+    from ddl_b200.config import Config
+    from ddl_b200.models import make_spec, oracle
+    from ddl_b200.models.cnn import Model
+    from ddl_b200.parallel.arena import make_arena
+    spec = make_spec("cnn", wm)
+    cfg = Config(batch_size=batch, keep_prob=keep_prob, seed=seed, backend="native")
+    params = make_arena(spec, "none", 1, dev())
+    grads = params.like()
+    init = oracle.init_params(spec, seed)
+    params.load_vars(init)
+    return spec, cfg, params, grads, init, Model(spec, params, grads, cfg, max_eval_batch=500)
+
+
+@pytest.mark.parametrize("keep_prob", [1.0, 0.5])
+def test_engine_gradients_match_oracle(keep_prob):
+    from ddl_b200.data import synthetic_mnist
+    from ddl_b200.models import oracle
+    spec, cfg, params, grads, init, model = _engine_setup(keep_prob=keep_prob)
+    assert model.backend == "native"
+    d = synthetic_mnist(300, 50, 9)
+    x, y = d.x_train[:100].to(dev()), d.y_train[:100].to(dev())
+    for step in (0, 3):
+        loss = model.compute_grads(x, y, step)
+        to_ref(None)
+        rl, rg, _ = oracle.loss_and_grads([p.to(dev()) for p in init], x, y, spec, keep_prob, None, cfg.seed, step)
+        assert abs(float(loss) - float(rl)) < 5e-3 * max(1.0, abs(float(rl)))
+        got = grads.views()
+        # tf32 products + fp32 accumulation through 7 layers forward and back: a few 1e-3 per op, plus
+        # the odd ReLU / pool-argmax flip near ties.  Direction must match tightly, magnitude loosely.
+        report = []
+        for i, (g, r) in enumerate(zip(got, rg)):
+            cos = float(F.cosine_similarity(g.flatten().double(), r.flatten().double(), dim=0))
+            report.append((i, rel_err(g, r), cos))
+        print("step", step, " ".join("v%d:%.1e/%.5f" % t for t in report))
+        for i, e, cos in report:
+            assert e < 8e-2 and cos > 0.998, "gradient v%d (step %d): rel %.3e cos %.5f" % (i, step, e, cos)
+
+
+def test_engine_eval_matches_oracle_and_odd_batches():
+    from ddl_b200.data import synthetic_mnist
+    from ddl_b200.models import oracle
+    spec, cfg, params, grads, init, model = _engine_setup()
+    d = synthetic_mnist(100, 1234, 9)
+    x, y = d.x_test.to(dev()), d.y_test.to(dev())
+    to_ref(None)
+    ref_logits = oracle.forward([p.to(dev()) for p in init], x, spec, 1.0)
+    logits = model.logits(x)                                 # 500 + 500 + 234 rows
+    assert rel_err(logits, ref_logits) < 1e-2
+    correct, n = model.evaluate(x, y)
+    ref_correct = int((ref_logits.argmax(1) == y.long()).sum())
+    assert n == 1234 and abs(correct - ref_correct) <= 3     # tf32 may flip near-ties
+
+
+def test_single_trainer_learns_on_gpu():
+    """SURVEY 7.3 minimum slice: P=1, W=1 on one GPU, native backend + fused optimizer kernel."""
+    from ddl_b200.config import Config
+    from ddl_b200.parallel.trainer import SPMDTrainer
+    cfg = Config(synthetic=True, synthetic_train=6000, synthetic_test=500, seed=1, lr=1e-3, eval_every=0,
+                 max_steps=60, log_time=False)
+    tr = SPMDTrainer(cfg, 0, 1, 0)
+    assert tr.model.backend == "native" and tr.transport.name == "local"
+    acc0 = tr.evaluate()
+    stats = tr.run()
+    assert stats["final_accuracy"] > max(0.5, acc0 + 0.2)     # the CPU/torch path reaches ~0.6 by step 40
