@@ -61,6 +61,21 @@ __device__ __forceinline__ void ddl_spin_guard(uint32_t& spins, uint64_t& t0) {
   }
 }
 
+// One elected lane of a fully converged warp (elect.sync).  Keeping the surrounding loop warp-uniform
+// and predicating only the single-thread instructions (TMA issue, tcgen05.mma, commit) lets ptxas
+// keep addresses and descriptors in uniform registers; an `if (lane == 0)` loop instead forces an
+// R2UR per operand and costs ~90 cycles per MMA issue (measured, profiles/tc_issue_latency.md).
+DDL_DEVICE bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, 0xffffffff;\n\t"
+      "@px mov.s32 %0, 1;\n\t}"
+      : "+r"(pred));
+  return pred != 0;
+}
+DDL_DEVICE int warp_id_uniform() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 DDL_DEVICE uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // Counter-based dropout hash.  Must stay bit-identical to ddl_b200/models/oracle.py:dropout_keep_mask.
@@ -96,10 +111,27 @@ DDL_DEVICE bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+DDL_DEVICE bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 DDL_DEVICE void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   uint64_t t0 = 0;
   while (!mbar_try_wait(bar, parity)) ddl_spin_guard(spins, t0);
+}
+// pure polling wait (no hardware suspend)
+DDL_DEVICE void mbar_wait_poll(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  while (!mbar_test_wait(bar, parity)) ddl_spin_guard(spins, t0);
 }
 
 // ------------------------------------------------------------------------------------ TMA

@@ -71,16 +71,20 @@ int alloc(DdlEngine* e, void** p, size_t bytes) {
   return 0;
 }
 
-// pick ntile (fprop needs %32, dgrad %16; we keep %32) and a K split so the grid has ~a wave of CTAs
+// Tile-shape policy (measured on B200, profiles/tc_issue_latency.md): the TMA engine feeds one SM at
+// ~80 B/clk and every k-iteration costs ~600 cycles of barrier + issue overhead, so (1) use the widest
+// N tile the layer allows - operand bytes per MAC fall as 1/N - and (2) get the CTA count from a
+// split over the reduction (taps x channel blocks), reduced with red.add, not from narrow N tiles.
 void pick_tiling(int pix_tiles, int nout, int kiters, bool allow_split, int* ntile, int* ksplit) {
-  int nt = nout >= 128 && nout % 128 == 0 ? 128 : (nout % 64 == 0 ? 64 : 32);
-  while (nt > 32 && pix_tiles * cdiv(nout, nt) < 120) nt /= 2;
-  int ctas = pix_tiles * cdiv(nout, nt);
+  int nt = 32;
+  for (int c : {256, 128, 64, 32}) if (nout % c == 0) { nt = c; break; }
+  const int ctas = pix_tiles * cdiv(nout, nt);
   int ks = 1;
-  if (allow_split && ctas < 96) {
-    ks = cdiv(132, ctas);
+  if (allow_split && ctas < 100) {
+    ks = (140 + ctas / 2) / ctas;
     if (ks > kiters / 4) ks = kiters / 4 > 0 ? kiters / 4 : 1;
-    if (ks > 8) ks = 8;
+    if (ks > 16) ks = 16;
+    if (ks < 1) ks = 1;
   }
   *ntile = nt; *ksplit = ks;
 }

@@ -23,6 +23,7 @@
 #include "../include/ddl_b200.h"
 
 #include <mutex>
+#include <stdlib.h>
 #include <new>
 
 namespace {
@@ -46,6 +47,8 @@ struct ActParams {
   int stages;
   int b_mn_major;                  // 1: weights [tap][cred][nout] (fprop), 0: [tap][nout][cred] (dgrad)
   int flags;
+  int debug;                       // perf experiments only: 1 = skip MMA issue, 2 = skip TMA loads
+  unsigned long long* trace;       // perf experiments only: per-iteration clock64 stamps of CTA (0,0,0)
   float* out;                      // [N*H*W, nout]
   const float* bias;               // [nout]
   const float* mask_act;           // [N*H*W, nout]; EPI_MASKPOS multiplies by (mask_act > 0) * mask_scale
@@ -96,7 +99,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const int stage_bytes = a_bytes + b_bytes;
   PipeBars* bars = (PipeBars*)(smem + (size_t)p.stages * stage_bytes);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
   const int tile = blockIdx.x;
   const int tw = tile % p.tiles_w, th = (tile / p.tiles_w) % p.tiles_h, tn = tile / (p.tiles_w * p.tiles_h);
   const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
@@ -121,53 +124,76 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const uint32_t tmem_base = bars->tmem_addr;
 
   if (warp == 0) {
-    // ================= TMA producer =================
-    if (lane == 0) {
-      const int box_rows = p.bw * p.bh * p.bn;
-      const uint32_t tx = (uint32_t)(box_rows * 128 + b_bytes);
-      const int half = p.ksize / 2;
-      for (int i = 0; i < niter; ++i) {
-        const int s = i % p.stages;
-        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
-        mbar_wait(&bars->empty[s], ph ^ 1u);
-        const int it = k_begin + i;
-        const int tap = it / p.cblocks, cb = it % p.cblocks;
+    // ================= TMA producer (warp-uniform loop, one elected lane issues) =================
+    const int box_rows = p.bw * p.bh * p.bn;
+    const uint32_t tx = (uint32_t)(box_rows * 128 + b_bytes);
+    const int half = p.ksize / 2;
+    int s = 0;
+    uint32_t ph = 0;
+    int tap = k_begin / p.cblocks, cb = k_begin % p.cblocks;
+    for (int i = 0; i < niter; ++i) {
+      const bool ptr = (p.debug & 8) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512;
+      if (ptr && lane == 0) p.trace[i * 4 + 0] = clock64();
+      mbar_wait(&bars->empty[s], ph ^ 1u);
+      if (elect_one()) {
+        if (ptr) p.trace[i * 4 + 1] = clock64();
+        if (!(p.debug & 8) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512) p.trace[i * 4 + 0] = clock64();
         int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
         if (p.flip) { dh = -dh; dw = -dw; }
         uint8_t* sa = smem + (size_t)s * stage_bytes;
         uint8_t* sb = sa + a_bytes;
-        mbar_expect_tx(&bars->full[s], tx);
-        tma_load_4d(sa, &map_act, &bars->full[s], cb * kKB, w0 + dw, h0 + dh, n0);
-        if (p.b_mn_major) {
-          for (int j = 0; j < p.ntile / 32; ++j)
-            tma_load_4d(sb + j * 4096, &map_w, &bars->full[s], nt0 + 32 * j, cb * kKB, tap, 0);
+        if (p.debug & 2) {
+          mbar_arrive(&bars->full[s]);
         } else {
-          tma_load_4d(sb, &map_w, &bars->full[s], cb * kKB, nt0, tap, 0);
+          mbar_expect_tx(&bars->full[s], tx);
+          if (ptr) p.trace[i * 4 + 2] = clock64();
+          tma_load_4d(sa, &map_act, &bars->full[s], cb * kKB, w0 + dw, h0 + dh, n0);
+          if (ptr) p.trace[i * 4 + 3] = clock64();
+          if (p.b_mn_major) {
+            for (int j = 0; j < p.ntile / 32; ++j)
+              tma_load_4d(sb + j * 4096, &map_w, &bars->full[s], nt0 + 32 * j, cb * kKB, tap, 0);
+          } else {
+            tma_load_4d(sb, &map_w, &bars->full[s], cb * kKB, nt0, tap, 0);
+          }
         }
       }
+      __syncwarp();
+      if (++cb == p.cblocks) { cb = 0; ++tap; }
+      if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_tf32(kTileM, p.ntile, 0, p.b_mn_major);
-      for (int i = 0; i < niter; ++i) {
-        const int s = i % p.stages;
-        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
-        mbar_wait(&bars->full[s], ph);
-        tc_fence_after();
-        const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+    // ================= MMA issuer (warp-uniform loop, one elected lane issues) =================
+    const uint32_t idesc = umma_idesc_tf32(kTileM, p.ntile, 0, p.b_mn_major);
+    const uint32_t smem_base = smem_u32(smem);
+    int s = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < niter; ++i) {
+      const bool tr = !(p.debug & 8) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512 && lane == 0;
+      if (tr) p.trace[i * 4 + 1] = clock64();
+      mbar_wait(&bars->full[s], ph);
+      if (tr) p.trace[i * 4 + 2] = clock64();
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sa = smem_base + (uint32_t)(s * stage_bytes);
         const uint32_t sb = sa + a_bytes;
+        if (!(p.debug & 1)) {
 #pragma unroll
-        for (int k = 0; k < kKB / kUmmaK; ++k) {
-          const uint64_t ad = umma_smem_desc(sa + k * 32, 16, 1024, DDL_UMMA_SW128);
-          const uint64_t bd = p.b_mn_major ? umma_smem_desc(sb + k * 1024, 4096, 512, DDL_UMMA_SW128_BASE32B)
-                                           : umma_smem_desc(sb + k * 32, 16, 1024, DDL_UMMA_SW128);
-          umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kKB / kUmmaK; ++k) {
+            const uint64_t ad = umma_smem_desc(sa + k * 32, 16, 1024, DDL_UMMA_SW128);
+            const uint64_t bd = p.b_mn_major ? umma_smem_desc(sb + k * 1024, 4096, 512, DDL_UMMA_SW128_BASE32B)
+                                             : umma_smem_desc(sb + k * 32, 16, 1024, DDL_UMMA_SW128);
+            umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
         }
         umma_commit(&bars->empty[s]);            // smem slot reusable once these MMAs have read it
+        if (i == niter - 1) umma_commit(&bars->tmem_full);   // accumulator complete
       }
-      umma_commit(&bars->tmem_full);             // accumulator complete
+      __syncwarp();
+      if (tr) p.trace[i * 4 + 3] = clock64();
+      if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
+    if (niter == 0 && elect_one()) umma_commit(&bars->tmem_full);
+    __syncwarp();
   } else {
     // ================= epilogue (warps 2..5) =================
     const int q = warp & 3;                      // TMEM lane quarter this warp may read
@@ -180,7 +206,8 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     const float* mrow = (p.flags & EPI_MASKPOS) ? p.mask_act + pix * p.nout + nt0 : nullptr;
     uint32_t seed = 0, stream = 0;
     if (p.flags & EPI_DROPOUT) { seed = p.st->seed; stream = p.st->stream + p.drop_stream_off; }
-    mbar_wait(&bars->tmem_full, 0);
+    if (lane == 0) mbar_wait(&bars->tmem_full, 0);      // one poller per warp: 128 threads hammering the
+    __syncwarp();                                        // same mbarrier slow the producer / MMA handoffs
     tc_fence_after();
     for (int c0 = 0; c0 < p.ntile; c0 += 16) {
       float v[16];
@@ -244,7 +271,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   const int stage_bytes = (a_boxes + b_boxes) * box_bytes;
   PipeBars* bars = (PipeBars*)(smem + (size_t)p.stages * stage_bytes);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
   const int tap = blockIdx.x;
   const int mt = blockIdx.y % p.mtiles, nt = blockIdx.y / p.mtiles;
   const int a0 = mt * kTileM, b0 = nt * p.ntile;
@@ -273,12 +300,12 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   const uint32_t tmem_base = bars->tmem_addr;
 
   if (warp == 0) {
-    if (lane == 0) {
-      const uint32_t tx = (uint32_t)((a_live + b_live) * box_bytes);
-      for (int i = 0; i < niter; ++i) {
-        const int s = i % p.stages;
-        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
-        mbar_wait(&bars->empty[s], ph ^ 1u);
+    const uint32_t tx = (uint32_t)((a_live + b_live) * box_bytes);
+    int s = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < niter; ++i) {
+      mbar_wait(&bars->empty[s], ph ^ 1u);
+      if (elect_one()) {
         const int t = t_begin + i;
         const int tw = t % p.tiles_w, th = (t / p.tiles_w) % p.tiles_h, tn = t / (p.tiles_w * p.tiles_h);
         const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
@@ -290,17 +317,20 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
         for (int j = 0; j < b_live; ++j)
           tma_load_4d(sb + j * box_bytes, &map_x, &bars->full[s], b0 + 32 * j, w0 + dw, h0 + dh, n0);
       }
+      __syncwarp();
+      if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_tf32(kTileM, p.ntile, 1, 1);
-      const int ksteps = R / kUmmaK;
-      for (int i = 0; i < niter; ++i) {
-        const int s = i % p.stages;
-        const uint32_t ph = (uint32_t)((i / p.stages) & 1);
-        mbar_wait(&bars->full[s], ph);
-        tc_fence_after();
-        const uint32_t sa = smem_u32(smem + (size_t)s * stage_bytes);
+    const uint32_t idesc = umma_idesc_tf32(kTileM, p.ntile, 1, 1);
+    const int ksteps = R / kUmmaK;
+    const uint32_t smem_base = smem_u32(smem);
+    int s = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < niter; ++i) {
+      mbar_wait(&bars->full[s], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sa = smem_base + (uint32_t)(s * stage_bytes);
         const uint32_t sb = sa + a_boxes * box_bytes;
         for (int k = 0; k < ksteps; ++k) {
           const uint64_t ad = umma_smem_desc(sa + k * 1024, (uint32_t)box_bytes, 512, DDL_UMMA_SW128_BASE32B);
@@ -308,15 +338,20 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
           umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
         }
         umma_commit(&bars->empty[s]);
+        if (i == niter - 1) umma_commit(&bars->tmem_full);
       }
-      umma_commit(&bars->tmem_full);
+      __syncwarp();
+      if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
+    if (niter == 0 && elect_one()) umma_commit(&bars->tmem_full);
+    __syncwarp();
   } else {
     const int q = warp & 3;
     const int a = a0 + q * 32 + lane;
     const bool valid = a < p.ca && niter > 0;
     float* obase = p.out + (int64_t)tap * p.cb * p.ca + a;
-    mbar_wait(&bars->tmem_full, 0);
+    if (lane == 0) mbar_wait(&bars->tmem_full, 0);      // one poller per warp: 128 threads hammering the
+    __syncwarp();                                        // same mbarrier slow the producer / MMA handoffs
     tc_fence_after();
     for (int c0 = 0; c0 < p.ntile; c0 += 16) {
       float v[16];
@@ -436,14 +471,24 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
   p.nout = nout; p.ntile = ntile;
   p.b_mn_major = dgrad ? 0 : 1;
   p.flags = flags | (p.ksplit > 1 ? EPI_ATOMIC : 0);
+  p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
+  p.trace = nullptr;
+  if (getenv("DDL_TC_TRACE")) {
+    cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long));
+    cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
+  }
   p.out = out; p.bias = bias; p.mask_act = mask_act; p.mask_scale = mask_scale;
   p.st = st; p.drop_stream_off = drop_stream_off;
   p.drop_thresh24 = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
   p.drop_inv_keep = keep_prob >= 1.f ? 1.f : 1.f / keep_prob;
   const int stage_bytes = kTileM * 128 + ntile * 128;
-  int stages = (200 * 1024) / stage_bytes;
+  // <= ~110 KB of stages: two CTAs per SM stay resident (grids of 150-300 CTAs run as one wave) and
+  // 4 stages already cover the ~1000-cycle TMA latency at ~600 cycles per k-iteration
+  int stages = (110 * 1024) / stage_bytes;
+  if (stages < 2) stages = 2;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages > p.kiters) stages = p.kiters < 2 ? 2 : p.kiters;
+  if (getenv("DDL_TC_STAGES")) stages = atoi(getenv("DDL_TC_STAGES"));
   p.stages = stages;
   pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
   pl->grid = dim3(p.tiles_w * p.tiles_h * p.tiles_n, ceil_div(nout, ntile), p.ksplit);
@@ -491,7 +536,7 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   const int ptiles = p.tiles_w * p.tiles_h * p.tiles_n;
   p.psplit = psplit < 1 ? 1 : (psplit > ptiles ? ptiles : psplit);
   const int stage_bytes = boxes * R * 128;
-  int stages = (200 * 1024) / stage_bytes;
+  int stages = (200 * 1024) / stage_bytes;           // wgrad grids are <= ~150 CTAs: one fat CTA per SM
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 1) { delete pl; return fail("stage does not fit in shared memory"); }
   p.stages = stages;
@@ -520,6 +565,13 @@ int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s) {
 }
 
 void ddl_tc_plan_destroy(DdlTcPlan* pl) { delete pl; }
+
+/* perf experiments: copies the clock64 trace of an act plan created under DDL_TC_TRACE=1 */
+int ddl_tc_plan_trace(const DdlTcPlan* pl, unsigned long long* host_out, int n) {
+  DDL_REQUIRE(pl && pl->kind == 0 && pl->act.trace, "no trace buffer");
+  DDL_CHECK_CUDA(cudaMemcpy(host_out, pl->act.trace, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return 0;
+}
 
 /* introspection for tests / profiling notes: fills {grid.x, grid.y, grid.z, stages, smem, bw, bh, bn} */
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8) {

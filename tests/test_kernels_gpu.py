@@ -242,13 +242,14 @@ def test_engine_eval_matches_oracle_and_odd_batches():
 
 
 def test_single_trainer_learns_on_gpu():
-    """SURVEY 7.3 minimum slice: P=1, W=1 on one GPU, native backend + fused optimizer kernel."""
+    """SURVEY 7.3 minimum slice: P=1, W=1 on one GPU: native engine + the K1 push/update kernel with zero
+    peers, CUDA-graph replay after two eager steps."""
     from ddl_b200.config import Config
     from ddl_b200.parallel.trainer import SPMDTrainer
     cfg = Config(synthetic=True, synthetic_train=6000, synthetic_test=500, seed=1, lr=1e-3, eval_every=0,
                  max_steps=60, log_time=False)
     tr = SPMDTrainer(cfg, 0, 1, 0)
-    assert tr.model.backend == "native" and tr.transport.name == "local"
+    assert tr.model.backend == "native" and tr.transport.name == "fused"
     acc0 = tr.evaluate()
     stats = tr.run()
     assert stats["final_accuracy"] > max(0.5, acc0 + 0.2)     # the CPU/torch path reaches ~0.6 by step 40

@@ -1,0 +1,22 @@
+import os, sys, ctypes as C
+os.environ["DDL_TC_TRACE"] = "1"; os.environ["DDL_TC_DEBUG"] = "8"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from ddl_b200.ops import native
+L = native.lib()
+L.ddl_tc_plan_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+dev = torch.device("cuda")
+N, cred, nout = 128, 2048, 32
+x = torch.randn(N, cred, device=dev); w = torch.randn(cred * nout, device=dev); out = torch.zeros(N, nout, device=dev)
+plan = L.ddl_tc_plan_act(0, x.data_ptr(), w.data_ptr(), out.data_ptr(), N, 1, 1, cred, nout, 1, 32, 1, 0, None, None, 1.0, None, 0, 1.0)
+for _ in range(3):
+    L.ddl_tc_plan_run(plan, native.stream_ptr())
+torch.cuda.synchronize()
+buf = (C.c_uint64 * (64 * 4))()
+L.ddl_tc_plan_trace(plan, buf, 64 * 4)
+t0 = buf[0]
+print("producer: before_wait after_wait after_expect_tx after_tma1 | wait expect tma1 rest_to_next")
+for i in range(24):
+    a, b, c, d = [buf[i*4+k]-t0 for k in range(4)]
+    nxt = buf[(i+1)*4]-t0
+    print(i, a, b, c, d, "| wait=%d expect=%d tma1=%d rest(tma2+sync+loop)=%d" % (b-a, c-b, d-c, nxt-d))
