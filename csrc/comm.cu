@@ -256,9 +256,11 @@ __global__ void device_barrier_kernel(const DdlComm c, uint32_t* epoch_counter) 
 }
 
 int comm_grid(int64_t elems) {
-  int64_t g = (elems / 4 + kCommThreads - 1) / kCommThreads;
+  // ~2 float4 per thread: the update is a latency-bound stream (7 arena-sized passes), so it wants
+  // every SM's full thread complement (4 x 512) rather than a long grid-stride loop.
+  int64_t g = (elems / 4 + 2 * kCommThreads - 1) / (2 * kCommThreads);
   if (g < 1) g = 1;
-  if (g > 148) g = 148;                 // one wave: every block is resident while it spins
+  if (g > 148 * 4) g = 148 * 4;
   return (int)g;
 }
 

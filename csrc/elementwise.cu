@@ -147,46 +147,41 @@ __global__ void conv1_relu_pool_kernel(const float* __restrict__ x, const float*
 }
 
 // conv1 weight / bias gradient.  dY is the full-resolution gradient [B,S,S,C] (after pool-bwd).
-// Block = 32 channels (x) by 8 pixel lanes; a thread keeps all 25 tap accumulators + the bias
-// accumulator in registers, so dY is read exactly once.  grid.x strides pixels, grid.y = C / 32.
-__global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restrict__ x,
+// One block = half an image (S/2 rows) x 32 channels: the dY tile and the zero-padded x halo are staged
+// in shared memory once, then warp t accumulates tap t (t = 25: the bias) with lane = channel, so the
+// inner loop is two LDS + one FMA per pixel.  grid = (2*B, C/32); block = 26 warps.
+__global__ void __launch_bounds__(832) conv1_wgrad_kernel(const float* __restrict__ x,
                                                           const float* __restrict__ dy,
                                                           float* __restrict__ dw, float* __restrict__ db,
                                                           int B, int S, int C) {
-  __shared__ float red[8][32];
-  const int c = blockIdx.y * 32 + (threadIdx.x & 31);
-  const int lane_p = threadIdx.x >> 5;
-  float acc[26];
-#pragma unroll
-  for (int i = 0; i < 26; ++i) acc[i] = 0.f;
-  const int64_t npix = (int64_t)B * S * S;
-  for (int64_t pix = (int64_t)blockIdx.x * 8 + lane_p; pix < npix; pix += (int64_t)gridDim.x * 8) {
-    float g = dy[pix * C + c];
-    int w0 = (int)(pix % S), h0 = (int)((pix / S) % S);
-    const float* xi = x + (pix / ((int64_t)S * S)) * S * S;
-    acc[25] += g;
-#pragma unroll
-    for (int kh = 0; kh < 5; ++kh) {
-      int h = h0 + kh - 2;
-#pragma unroll
-      for (int kw = 0; kw < 5; ++kw) {
-        int ww = w0 + kw - 2;
-        float xv = (h >= 0 && h < S && ww >= 0 && ww < S) ? __ldg(xi + h * S + ww) : 0.f;
-        acc[kh * 5 + kw] += xv * g;
-      }
-    }
+  extern __shared__ float sm[];
+  const int rows = S / 2, XP = S + 4;
+  float* sdy = sm;                               // [rows*S][32]
+  float* sx = sm + rows * S * 32;                // [(rows+4)][S+4], zero padded
+  const int n = blockIdx.x >> 1, half = blockIdx.x & 1;
+  const int h0 = half * rows, cg = blockIdx.y * 32;
+  const int lane = threadIdx.x & 31, tap = threadIdx.x >> 5;
+  const float* dyi = dy + ((int64_t)n * S * S + (int64_t)h0 * S) * C + cg;
+  for (int i = threadIdx.x; i < rows * S * 32; i += blockDim.x)
+    sdy[i] = dyi[(int64_t)(i >> 5) * C + (i & 31)];
+  for (int i = threadIdx.x; i < (rows + 4) * XP; i += blockDim.x) {
+    const int r = i / XP + h0 - 2, cc = i % XP - 2;
+    sx[i] = (r >= 0 && r < S && cc >= 0 && cc < S) ? x[(int64_t)n * S * S + r * S + cc] : 0.f;
   }
-#pragma unroll
-  for (int i = 0; i < 26; ++i) {
-    red[lane_p][threadIdx.x & 31] = acc[i];
-    __syncthreads();
-    if (lane_p == 0) {
-      float s2 = 0.f;
-#pragma unroll
-      for (int l = 0; l < 8; ++l) s2 += red[l][threadIdx.x & 31];
-      if (i < 25) atomicAdd(dw + i * C + c, s2); else atomicAdd(db + c, s2);
+  __syncthreads();
+  float acc = 0.f;
+  if (tap < 25) {
+    const int kh = tap / 5, kw = tap % 5;
+    for (int py = 0; py < rows; ++py) {
+      const float* xr = sx + (py + kh) * XP + kw;
+      const float* gr = sdy + py * S * 32 + lane;
+#pragma unroll 4
+      for (int px = 0; px < S; ++px) acc += xr[px] * gr[px * 32];
     }
-    __syncthreads();
+    atomicAdd(dw + tap * C + cg + lane, acc);
+  } else {
+    for (int i = 0; i < rows * S; ++i) acc += sdy[i * 32 + lane];
+    atomicAdd(db + cg + lane, acc);
   }
 }
 
@@ -288,19 +283,36 @@ __global__ void colsum_kernel(const float* __restrict__ x, float* __restrict__ o
 __global__ void fc3_xent_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w,
                                     const float* __restrict__ bias, const int* __restrict__ labels,
                                     float* __restrict__ logits, float* __restrict__ dlogits,
-                                    DdlStepState* st, int B, int K, int NC, float scale) {
+                                    DdlStepState* st, int B, int K, int NC, float scale, int use_smem) {
+  extern __shared__ float sw3[];            // [K][NC] when use_smem
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (use_smem) {
+    for (int i = threadIdx.x; i < K * NC; i += blockDim.x) sw3[i] = w[i];
+    __syncthreads();
+  }
   if (row >= B) return;
+  const float* wsrc = use_smem ? sw3 : w;
   float acc[16];
 #pragma unroll
   for (int c = 0; c < 16; ++c) acc[c] = 0.f;
-  for (int k = lane; k < K; k += 32) {
-    float hv = h[(int64_t)row * K + k];
-    const float* wr = w + (int64_t)k * NC;
+  for (int kb = 0; kb < K; kb += 32 * 8) {                 // 8 independent h loads in flight per lane
+    float hv[8];
 #pragma unroll
-    for (int c = 0; c < 16; ++c)
-      if (c < NC) acc[c] += hv * __ldg(wr + c);
+    for (int u = 0; u < 8; ++u) {
+      const int k = kb + u * 32 + lane;
+      hv[u] = k < K ? h[(int64_t)row * K + k] : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int k = kb + u * 32 + lane;
+      if (k < K) {
+        const float* wr = wsrc + (int64_t)k * NC;
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+          if (c < NC) acc[c] += hv[u] * wr[c];
+      }
+    }
   }
   float z = -INFINITY;
 #pragma unroll
@@ -334,9 +346,11 @@ __global__ void fc3_xent_fwd_kernel(const float* __restrict__ h, const float* __
 // grid.x = ceil(K / 32): a block owns 32 k-columns of h, staged in smem with dl.
 __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w,
                                const float* __restrict__ dl, float* __restrict__ dw, float* __restrict__ db,
-                               float* __restrict__ dh, int B, int K, int NC, uint32_t seed, uint32_t stream,
-                               uint32_t thresh24, float inv_keep, const DdlStepState* st) {
+                               float* __restrict__ dh, float* __restrict__ dbh, int B, int K, int NC,
+                               uint32_t seed, uint32_t stream, uint32_t thresh24, float inv_keep,
+                               const DdlStepState* st) {
   extern __shared__ float sm[];
+  __shared__ float colred[8][32];
   if (st) { seed = st->seed; stream += st->stream; }
   float* sdl = sm;                        // [B][NC]
   float* sh = sm + B * NC;                // [B][32]
@@ -367,6 +381,7 @@ __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restr
       db[c] += s2;
     }
   }
+  float colsum = 0.f;                      // blockDim.x is a multiple of 32: a thread keeps one column
   for (int t = threadIdx.x; t < B * 32; t += blockDim.x) {
     int r = t >> 5, ks = t & 31, k = k0 + ks;
     if (k >= K) continue;
@@ -374,7 +389,18 @@ __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restr
     for (int cc = 0; cc < NC; ++cc) s2 += sdl[r * NC + cc] * sw[ks * NC + cc];
     uint32_t e = (uint32_t)(r * K + k);
     bool keep = thresh24 >= (1u << 24) || ddl_dropout_keep(seed, stream, e, thresh24);
-    dh[(int64_t)r * K + k] = keep ? s2 * inv_keep : 0.f;
+    const float o = keep ? s2 * inv_keep : 0.f;
+    dh[(int64_t)r * K + k] = o;
+    colsum += o;
+  }
+  if (dbh) {                                // bias gradient of the layer that produced h: sum_r dh[r, k]
+    colred[threadIdx.x >> 5][threadIdx.x & 31] = colsum;
+    __syncthreads();
+    if (threadIdx.x < 32 && k0 + threadIdx.x < K) {
+      float t2 = 0.f;
+      for (int l = 0; l < (int)(blockDim.x >> 5); ++l) t2 += colred[l][threadIdx.x];
+      dbh[k0 + threadIdx.x] += t2;
+    }
   }
 }
 
@@ -430,8 +456,16 @@ int ddl_conv1_relu_pool(const float* x, const float* w, const float* bias, float
 
 int ddl_conv1_wgrad(const float* x, const float* dy, float* dw, float* db, int B, int S, int C, cudaStream_t s) {
   DDL_REQUIRE(C % 32 == 0, "ddl_conv1_wgrad: C %% 32 == 0");
-  dim3 grid(148 * 2, C / 32);
-  conv1_wgrad_kernel<<<grid, 256, 0, s>>>(x, dy, dw, db, B, S, C);
+  DDL_REQUIRE(S % 2 == 0, "ddl_conv1_wgrad: S must be even");
+  dim3 grid(2 * B, C / 32);
+  const size_t smem = ((size_t)(S / 2) * S * 32 + (size_t)(S / 2 + 4) * (S + 4)) * sizeof(float);
+  static bool attr_done = false;
+  if (!attr_done) {
+    DDL_CHECK_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    attr_done = true;
+  }
+  DDL_REQUIRE(smem <= 100 * 1024, "ddl_conv1_wgrad: tile does not fit shared memory");
+  conv1_wgrad_kernel<<<grid, 832, smem, s>>>(x, dy, dw, db, B, S, C);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -464,20 +498,23 @@ int ddl_colsum(const float* x, float* out, int R, int C, cudaStream_t s) {
 int ddl_fc3_xent_fwd(const float* h, const float* w, const float* bias, const int* labels, float* logits,
                      float* dlogits, DdlStepState* st, int B, int K, int NC, float scale, cudaStream_t s) {
   DDL_REQUIRE(NC <= 16, "ddl_fc3_xent_fwd: at most 16 classes");
-  fc3_xent_fwd_kernel<<<(B + 7) / 8, 256, 0, s>>>(h, w, bias, labels, logits, dlogits, st, B, K, NC, scale);
+  const size_t wbytes = (size_t)K * NC * sizeof(float);
+  const int use_smem = wbytes <= 48 * 1024 ? 1 : 0;
+  fc3_xent_fwd_kernel<<<(B + 7) / 8, 256, use_smem ? wbytes : 0, s>>>(h, w, bias, labels, logits, dlogits, st, B, K,
+                                                                       NC, scale, use_smem);
   DDL_LAUNCH_CHECK();
   return 0;
 }
 
-static int fc3_bwd_launch(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, int B,
-                          int K, int NC, uint32_t seed, uint32_t stream, const DdlStepState* st, float keep_prob,
-                          cudaStream_t s) {
+static int fc3_bwd_launch(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh,
+                          float* dbh, int B, int K, int NC, uint32_t seed, uint32_t stream, const DdlStepState* st,
+                          float keep_prob, cudaStream_t s) {
   size_t smem = ((size_t)B * (NC + 32) + 32 * NC) * sizeof(float);
   DDL_REQUIRE(NC <= 32 && smem <= 200 * 1024, "ddl_fc3_bwd: batch %d too large for smem staging", B);
   uint32_t thresh = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
   if (smem > 48 * 1024)
     DDL_CHECK_CUDA(cudaFuncSetAttribute(fc3_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  fc3_bwd_kernel<<<(K + 31) / 32, 256, smem, s>>>(h, w, dl, dw, db, dh, B, K, NC, seed, stream, thresh,
+  fc3_bwd_kernel<<<(K + 31) / 32, 256, smem, s>>>(h, w, dl, dw, db, dh, dbh, B, K, NC, seed, stream, thresh,
                                                  keep_prob >= 1.f ? 1.f : 1.f / keep_prob, st);
   DDL_LAUNCH_CHECK();
   return 0;
@@ -485,12 +522,13 @@ static int fc3_bwd_launch(const float* h, const float* w, const float* dl, float
 
 int ddl_fc3_bwd(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, int B, int K,
                 int NC, uint32_t seed, uint32_t stream, float keep_prob, cudaStream_t s) {
-  return fc3_bwd_launch(h, w, dl, dw, db, dh, B, K, NC, seed, stream, nullptr, keep_prob, s);
+  return fc3_bwd_launch(h, w, dl, dw, db, dh, nullptr, B, K, NC, seed, stream, nullptr, keep_prob, s);
 }
 
-int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, int B, int K,
-                   int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob, cudaStream_t s) {
-  return fc3_bwd_launch(h, w, dl, dw, db, dh, B, K, NC, 0, stream_off, st, keep_prob, s);
+int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, float* dbh,
+                   int B, int K, int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob,
+                   cudaStream_t s) {
+  return fc3_bwd_launch(h, w, dl, dw, db, dh, dbh, B, K, NC, 0, stream_off, st, keep_prob, s);
 }
 
 int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int B, int NC, cudaStream_t s) {

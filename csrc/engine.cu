@@ -104,13 +104,13 @@ int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
     const int S = e->S[l], cin = e->C[l], cout = e->C[l + 1];
     // probe the pixel tiling with a throw-away plan to size ntile / ksplit
     DdlTcPlan* probe = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, 32, 1, 0,
-                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
     if (!probe) return -1;
     int nt, ks;
     pick_tiling(pix_tiles_of(probe), cout, 25 * cdiv(cin, 32), true, &nt, &ks);
     ddl_tc_plan_destroy(probe);
     out->conv[l - 1] = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, nt, ks, 0,
-                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
     if (!out->conv[l - 1]) return -1;
     out->conv_split[l - 1] = ks;
   }
@@ -120,11 +120,11 @@ int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
   const int drop = (train && c.keep_prob < 1.f) ? 4 : 0;
   if (e->nconv) {
     out->fc[0] = ddl_tc_plan_act(0, fc_in, e->P(vf), e->h1, B, 1, 1, e->F[0], e->F[1], 1, 32, 1, 1 | 2 | drop,
-                                 e->P(vf + 1), nullptr, 1.f, train ? c.st : nullptr, 0, kp);
+                                 e->P(vf + 1), nullptr, 1.f, train ? c.st : nullptr, 0, kp, nullptr);
     if (!out->fc[0]) return -1;
   }
   out->fc[1] = ddl_tc_plan_act(0, e->h1, e->P(vf + 2), e->h2, B, 1, 1, e->F[1], e->F[2], 1, 32, 1, 1 | drop,
-                               e->P(vf + 3), nullptr, 1.f, train ? c.st : nullptr, 1, kp);
+                               e->P(vf + 3), nullptr, 1.f, train ? c.st : nullptr, 1, kp, nullptr);
   if (!out->fc[1]) return -1;
   return 0;
 }
@@ -136,13 +136,14 @@ int build_bwd(DdlEngine* e) {
   const float inv_keep = c.keep_prob < 1.f ? 1.f / c.keep_prob : 1.f;
   // fc2: dW2 = h1^T dh2 ; dh1 = (dh2 W2^T) * (h1 > 0) / keep
   e->wg_fc[1] = ddl_tc_plan_wgrad(e->dh2, e->h1, e->G(vf + 2), B, 1, 1, e->F[2], e->F[1], 1, 64, 1);
+  // its epilogue also reduces the columns of dh1 into the fc1 bias gradient
   e->dg_fc[1] = ddl_tc_plan_act(1, e->dh2, e->P(vf + 2), e->dh1, B, 1, 1, e->F[2], e->F[1], 1, 32, 1, 8, nullptr,
-                                e->h1, inv_keep, nullptr, 0, 1.f);
+                                e->h1, inv_keep, nullptr, 0, 1.f, e->G(vf + 1));
   if (!e->wg_fc[1] || !e->dg_fc[1]) return -1;
   if (e->nconv) {
     e->wg_fc[0] = ddl_tc_plan_wgrad(e->dh1, e->pooled[3], e->G(vf), B, 1, 1, e->F[1], e->F[0], 1, 64, 1);
     e->dg_fc[0] = ddl_tc_plan_act(1, e->dh1, e->P(vf), e->dpool[3], B, 1, 1, e->F[1], e->F[0], 1, 32, 1, 0, nullptr,
-                                  nullptr, 1.f, nullptr, 0, 1.f);
+                                  nullptr, 1.f, nullptr, 0, 1.f, nullptr);
     if (!e->wg_fc[0] || !e->dg_fc[0]) return -1;
   }
   int v = 2;
@@ -160,13 +161,13 @@ int build_bwd(DdlEngine* e) {
     if (!e->wg_conv[l - 1]) return -1;
     // dgrad: dp_{l-1}[pix, cin] = sum_{tap, cout} dY[pix - off, cout] * W[tap][cin][cout]
     DdlTcPlan* probe2 = ddl_tc_plan_act(1, e->dfull, e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, 32, 1, 0,
-                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
     if (!probe2) return -1;
     int nt, ks;
     pick_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), true, &nt, &ks);
     ddl_tc_plan_destroy(probe2);
     e->dg_conv[l - 1] = ddl_tc_plan_act(1, e->dfull, e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, nt, ks, 0,
-                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f);
+                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
     if (!e->dg_conv[l - 1]) return -1;
     e->dg_split[l - 1] = ks;
   }
@@ -275,13 +276,12 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   if (ddl_fc3_xent_fwd(e->h2, e->P(vf + 4), e->P(vf + 5), y, nullptr, e->dlogits, c.st, B, e->F[2], e->F[3],
                        1.f / (float)B, s)) return -1;
   // ---- backward
-  if (ddl_fc3_bwd_st(e->h2, e->P(vf + 4), e->dlogits, e->G(vf + 4), e->G(vf + 5), e->dh2, B, e->F[2], e->F[3],
-                     c.st, 1, c.keep_prob, s)) return -1;
+  // fc3 backward also emits the fc2 bias gradient (column sums of dh2)
+  if (ddl_fc3_bwd_st(e->h2, e->P(vf + 4), e->dlogits, e->G(vf + 4), e->G(vf + 5), e->dh2, e->G(vf + 3), B, e->F[2],
+                     e->F[3], c.st, 1, c.keep_prob, s)) return -1;
   if (ddl_tc_plan_run(e->wg_fc[1], s)) return -1;
-  if (ddl_colsum(e->dh2, e->G(vf + 3), B, e->F[2], s)) return -1;
-  if (ddl_tc_plan_run(e->dg_fc[1], s)) return -1;
+  if (ddl_tc_plan_run(e->dg_fc[1], s)) return -1;      // + fc1 bias gradient in its epilogue
   if (ddl_tc_plan_run(e->wg_fc[0], s)) return -1;
-  if (ddl_colsum(e->dh1, e->G(vf + 1), B, e->F[1], s)) return -1;
   if (ddl_tc_plan_run(e->dg_fc[0], s)) return -1;
   int v = 6;
   for (int l = 3; l >= 1; --l, v -= 2) {           // conv4, conv3, conv2

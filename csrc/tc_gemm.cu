@@ -51,6 +51,7 @@ struct ActParams {
   unsigned long long* trace;       // perf experiments only: per-iteration clock64 stamps of CTA (0,0,0)
   float* out;                      // [N*H*W, nout]
   const float* bias;               // [nout]
+  float* colsum;                   // [nout]; EPI_COLSUM adds the column sums of the final values (bias gradient)
   const float* mask_act;           // [N*H*W, nout]; EPI_MASKPOS multiplies by (mask_act > 0) * mask_scale
   float mask_scale;
   const DdlStepState* st;          // dropout seed / stream
@@ -71,7 +72,7 @@ struct WgradParams {
   float* out;                      // [taps][cb][ca], accumulated with red.add
 };
 
-enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16 };
+enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16, EPI_COLSUM = 32 };
 
 struct alignas(8) PipeBars {
   uint64_t full[kMaxStages];
@@ -212,11 +213,12 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     for (int c0 = 0; c0 < p.ntile; c0 += 16) {
       float v[16];
       tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-      if (!valid) continue;
       if (p.flags & EPI_ATOMIC) {
+        if (valid) {
 #pragma unroll
-        for (int j = 0; j < 16; j += 4) {
-          if (nt0 + c0 + j < p.nout) red_add_v4_f32(orow + c0 + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+          for (int j = 0; j < 16; j += 4) {
+            if (nt0 + c0 + j < p.nout) red_add_v4_f32(orow + c0 + j, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+          }
         }
         continue;
       }
@@ -232,7 +234,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
         }
         v[j] = x;
       }
-      if (p.flags & EPI_MASKPOS) {
+      if ((p.flags & EPI_MASKPOS) && valid) {
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
           if (nt0 + c0 + j < p.nout) {
@@ -244,10 +246,21 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
           }
         }
       }
+      if (p.flags & EPI_COLSUM) {              // warp-wide column sums of this warp's 32 rows
 #pragma unroll
-      for (int j = 0; j < 16; j += 4) {
-        if (nt0 + c0 + j < p.nout)
-          *reinterpret_cast<float4*>(orow + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        for (int j = 0; j < 16; ++j) {
+          float sv = valid ? v[j] : 0.f;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) sv += __shfl_xor_sync(0xffffffffu, sv, o);
+          if (lane == j && nt0 + c0 + j < p.nout) atomicAdd(p.colsum + nt0 + c0 + j, sv);
+        }
+      }
+      if (valid) {
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) {
+          if (nt0 + c0 + j < p.nout)
+            *reinterpret_cast<float4*>(orow + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
       }
     }
   }
@@ -451,7 +464,7 @@ extern "C" {
 DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
                            int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
                            const float* mask_act, float mask_scale, const DdlStepState* st,
-                           uint32_t drop_stream_off, float keep_prob) {
+                           uint32_t drop_stream_off, float keep_prob, float* colsum) {
   auto fail = [](const char* why) -> DdlTcPlan* { ddl::set_error("ddl_tc_plan_act: %s", why); return nullptr; };
   if (cred % 4 || nout % 4) return fail("channel counts must be multiples of 4 (16-byte TMA pitch)");
   if (ntile < 16 || ntile > 256 || ntile % 16) return fail("ntile must be a multiple of 16 in [16, 256]");
@@ -478,6 +491,9 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
     cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
   }
   p.out = out; p.bias = bias; p.mask_act = mask_act; p.mask_scale = mask_scale;
+  p.colsum = colsum;
+  if (colsum) p.flags |= EPI_COLSUM;
+  if ((p.flags & EPI_COLSUM) && (p.flags & EPI_ATOMIC)) return (delete pl, fail("column sums need an unsplit reduction"));
   p.st = st; p.drop_stream_off = drop_stream_off;
   p.drop_thresh24 = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
   p.drop_inv_keep = keep_prob >= 1.f ? 1.f : 1.f / keep_prob;

@@ -65,7 +65,7 @@ class NativeBackend:
         advanced (``advance_state``) by the caller."""
         native.check(self.L.ddl_engine_train_step(self.h, native.ptr(x), native.ptr(y), native.stream_ptr()),
                      "ddl_engine_train_step")
-        native.count(28)
+        native.count(26)
 
     def advance_state(self, advance_opt: bool = True) -> None:
         c = self.cfg

@@ -69,8 +69,10 @@ int ddl_fc3_xent_fwd(const float* h, const float* w, const float* bias, const in
 int ddl_fc3_bwd(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, int B, int K,
                 int NC, uint32_t seed, uint32_t stream, float keep_prob, cudaStream_t s);
 /* same, dropout seed/stream read from the device step state (graph-replay safe) */
-int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, int B, int K,
-                   int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob, cudaStream_t s);
+/* dbh (may be NULL): += column sums of dh = bias gradient of the layer that produced h */
+int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, float* dbh,
+                   int B, int K, int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob,
+                   cudaStream_t s);
 int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int B, int NC, cudaStream_t s);
 
 /* ---- tcgen05 implicit-GEMM plans (csrc/tc_gemm.cu) ------------------------------------------
@@ -81,12 +83,13 @@ int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int 
  *   act plan, dgrad=1: out[pix,n] = epi(sum_{tap,c} act[pix-off(tap), c] * w[tap][n][c])
  *   wgrad plan:        out[tap][b][a] += sum_pix g[pix,a] * x[pix+off(tap), b]
  * flags: 1 bias, 2 relu, 4 dropout (seed/stream from st), 8 multiply by (mask_act > 0) * mask_scale.
- * ksplit > 1 accumulates raw sums with red.add into a pre-zeroed out (no bias/relu/dropout). */
+ * ksplit > 1 accumulates raw sums with red.add into a pre-zeroed out (no bias/relu/dropout).
+ * colsum (may be NULL): += per-column sums of the final output values (a bias gradient). */
 typedef struct DdlTcPlan DdlTcPlan;
 DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
                            int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
                            const float* mask_act, float mask_scale, const DdlStepState* st,
-                           uint32_t drop_stream_off, float keep_prob);
+                           uint32_t drop_stream_off, float keep_prob, float* colsum);
 DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,
                              int ksize, int ntile, int psplit);
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);

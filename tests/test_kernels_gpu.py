@@ -145,8 +145,11 @@ def test_tc_linear_fwd_dx_dw(B, Kin, N):
     dx = K.linear_dx(dy, w)
     assert rel_err(dx, (dy.double() @ w.double().t()).float()) < TF32_TOL
     act = torch.randn(B, Kin, device=dev())
-    dxm = K.linear_dx(dy, w, act, 2.0)
-    assert rel_err(dxm, ((dy.double() @ w.double().t()) * (act > 0) * 2.0).float()) < TF32_TOL
+    cs = torch.zeros(Kin, device=dev())
+    dxm = K.linear_dx(dy, w, act, 2.0, colsum=cs)
+    refm = ((dy.double() @ w.double().t()) * (act > 0) * 2.0).float()
+    assert rel_err(dxm, refm) < TF32_TOL
+    assert rel_err(cs, refm.sum(0)) < TF32_TOL             # fused bias-gradient reduction
     dw = K.linear_dw(dy, x)
     assert rel_err(dw, (x.double().t() @ dy.double()).float()) < TF32_TOL
 

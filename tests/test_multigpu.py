@@ -1,0 +1,23 @@
+"""Distributed tier, GPU: the fused peer-memory transport on >= 2 GPUs of one box.
+Sync: workers bitwise-equal after every step and equal to the NCCL rung; async: no lost updates."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def run_case(case, nproc=2, timeout=300):
+    port = 29600 + (abs(hash(case)) % 200)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py"), case]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    assert r.returncode == 0 and "MGPU_OK " + case in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "async_sgd", "async_adam", "async_train"])
+def test_fused_transport(case):
+    run_case(case)
