@@ -41,7 +41,9 @@ struct DdlEngine {
   float* pooled[4] = {};           // p1..p4  [B, S[i+1], S[i+1], C[i+1]]
   uint8_t* idx[4] = {};
   float* raw = nullptr;            // raw conv sums, reused by conv2..4  [B, S, S, Cout] max
-  float* dfull = nullptr;          // full-resolution gradient dY, reused   [B, S, S, Cout] max
+  float* dfull[4] = {};            // full-resolution gradients dY of conv1..conv4 [B, S, S, Cout]: one buffer
+                                   // per layer, because layer l's wgrad (side stream) still reads its dY while
+                                   // the main stream is already producing layer l-1's
   float* dpool[4] = {};            // gradient wrt pooled outputs p1..p4
   float* h1 = nullptr;             // fc1 output after ReLU + dropout [B, F1]
   float* h2 = nullptr;             // fc2 output after dropout        [B, F2]
@@ -58,6 +60,11 @@ struct DdlEngine {
   DdlTcPlan* wg_fc[2] = {};
   DdlTcPlan* dg_fc[2] = {};        // dg_fc[0]: fc1 -> dp4 (cnn only), dg_fc[1]: fc2 -> dh1
   std::vector<void*> allocs;
+  // fork/join: weight-gradient kernels run on a side stream next to the dgrad chain (they only feed the
+  // optimizer); captured into the step graph as parallel branches
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork[8] = {};
+  cudaEvent_t ev_join = nullptr;
 
   const float* P(int v) const { return cfg.params + cfg.var_offset[v]; }
   float* G(int v) const { return cfg.grads + cfg.var_offset[v]; }
@@ -150,23 +157,23 @@ int build_bwd(DdlEngine* e) {
   for (int l = 1; l < e->nconv; ++l, v += 2) {
     const int S = e->S[l], cin = e->C[l], cout = e->C[l + 1];
     const int nt_w = cin >= 128 ? 128 : (cin >= 64 ? 64 : 32);
-    DdlTcPlan* probe = ddl_tc_plan_wgrad(e->dfull, e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, 1);
+    DdlTcPlan* probe = ddl_tc_plan_wgrad(e->dfull[l], e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, 1);
     if (!probe) return -1;
     int info[8];
     ddl_tc_plan_info(probe, info);
     ddl_tc_plan_destroy(probe);
     int base = info[0] * info[1];
     int psplit = base >= 120 ? 1 : cdiv(148, base);
-    e->wg_conv[l - 1] = ddl_tc_plan_wgrad(e->dfull, e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, psplit);
+    e->wg_conv[l - 1] = ddl_tc_plan_wgrad(e->dfull[l], e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, psplit);
     if (!e->wg_conv[l - 1]) return -1;
     // dgrad: dp_{l-1}[pix, cin] = sum_{tap, cout} dY[pix - off, cout] * W[tap][cin][cout]
-    DdlTcPlan* probe2 = ddl_tc_plan_act(1, e->dfull, e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, 32, 1, 0,
+    DdlTcPlan* probe2 = ddl_tc_plan_act(1, e->dfull[l], e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, 32, 1, 0,
                                         nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
     if (!probe2) return -1;
     int nt, ks;
     pick_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), true, &nt, &ks);
     ddl_tc_plan_destroy(probe2);
-    e->dg_conv[l - 1] = ddl_tc_plan_act(1, e->dfull, e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, nt, ks, 0,
+    e->dg_conv[l - 1] = ddl_tc_plan_act(1, e->dfull[l], e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, nt, ks, 0,
                                         nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
     if (!e->dg_conv[l - 1]) return -1;
     e->dg_split[l - 1] = ks;
@@ -235,11 +242,13 @@ DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg) {
     if (alloc(e, (void**)&e->idx[l], (size_t)cfg->batch * e->S[l + 1] * e->S[l + 1] * e->C[l + 1])) return fail(e, nullptr);
     if (alloc(e, (void**)&e->dpool[l], (size_t)cfg->batch * e->S[l + 1] * e->S[l + 1] * e->C[l + 1] * 4)) return fail(e, nullptr);
   }
-  const size_t full_train = (size_t)cfg->batch * e->S[0] * e->S[0] * e->C[1] > (size_t)cfg->batch * e->S[1] * e->S[1] * e->C[2]
-                                ? (size_t)cfg->batch * e->S[0] * e->S[0] * e->C[1]
-                                : (size_t)cfg->batch * e->S[1] * e->S[1] * e->C[2];
   if (alloc(e, (void**)&e->raw, full_max * 4)) return fail(e, nullptr);
-  if (alloc(e, (void**)&e->dfull, full_train * 4)) return fail(e, nullptr);
+  for (int l = 0; l < 4; ++l)
+    if (alloc(e, (void**)&e->dfull[l], (size_t)cfg->batch * e->S[l] * e->S[l] * e->C[l + 1] * 4)) return fail(e, nullptr);
+  if (cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking) != cudaSuccess) return fail(e, "side stream");
+  for (auto& ev : e->ev_fork)
+    if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
+  if (cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   if (alloc(e, (void**)&e->h1, mb * e->F[1] * 4) || alloc(e, (void**)&e->h2, mb * e->F[2] * 4) ||
       alloc(e, (void**)&e->dh1, (size_t)cfg->batch * e->F[1] * 4) || alloc(e, (void**)&e->dh2, (size_t)cfg->batch * e->F[2] * 4) ||
       alloc(e, (void**)&e->logits, mb * 16 * 4) || alloc(e, (void**)&e->dlogits, (size_t)cfg->batch * 16 * 4) ||
@@ -260,6 +269,9 @@ void ddl_engine_destroy(DdlEngine* e) {
   for (auto& p : e->wg_fc) ddl_tc_plan_destroy(p);
   for (auto& p : e->dg_fc) ddl_tc_plan_destroy(p);
   for (void* p : e->allocs) cudaFree(p);
+  for (auto& ev : e->ev_fork) if (ev) cudaEventDestroy(ev);
+  if (e->ev_join) cudaEventDestroy(e->ev_join);
+  if (e->side) cudaStreamDestroy(e->side);
   delete e;
 }
 
@@ -279,21 +291,36 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   // fc3 backward also emits the fc2 bias gradient (column sums of dh2)
   if (ddl_fc3_bwd_st(e->h2, e->P(vf + 4), e->dlogits, e->G(vf + 4), e->G(vf + 5), e->dh2, e->G(vf + 3), B, e->F[2],
                      e->F[3], c.st, 1, c.keep_prob, s)) return -1;
-  if (ddl_tc_plan_run(e->wg_fc[1], s)) return -1;
+  // Main stream: the data-gradient chain.  Side stream: every weight-gradient GEMM, forked as soon as its
+  // dY exists and joined once before the optimizer.
+  cudaStream_t w = e->side;
+  int fk = 0;
+  auto fork = [&]() -> int {
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork[fk], s));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(w, e->ev_fork[fk], 0));
+    ++fk;
+    return 0;
+  };
+  if (fork()) return -1;
+  if (ddl_tc_plan_run(e->wg_fc[1], w)) return -1;
   if (ddl_tc_plan_run(e->dg_fc[1], s)) return -1;      // + fc1 bias gradient in its epilogue
-  if (ddl_tc_plan_run(e->wg_fc[0], s)) return -1;
+  if (fork()) return -1;
+  if (ddl_tc_plan_run(e->wg_fc[0], w)) return -1;
   if (ddl_tc_plan_run(e->dg_fc[0], s)) return -1;
   int v = 6;
   for (int l = 3; l >= 1; --l, v -= 2) {           // conv4, conv3, conv2
     const int S = e->S[l], cout = e->C[l + 1], cin = e->C[l];
-    if (ddl_maxpool_bwd(e->dpool[l], e->idx[l], e->dfull, e->G(v + 1), B, S, S, cout, s)) return -1;
-    if (ddl_tc_plan_run(e->wg_conv[l - 1], s)) return -1;
     if (e->dg_split[l - 1] > 1)
       DDL_CHECK_CUDA(cudaMemsetAsync(e->dpool[l - 1], 0, (size_t)B * S * S * cin * sizeof(float), s));
+    if (ddl_maxpool_bwd(e->dpool[l], e->idx[l], e->dfull[l], e->G(v + 1), B, S, S, cout, s)) return -1;
+    if (fork()) return -1;
+    if (ddl_tc_plan_run(e->wg_conv[l - 1], w)) return -1;
     if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
   }
-  if (ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull, nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
-  if (ddl_conv1_wgrad(x, e->dfull, e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
+  if (ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull[0], nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
+  if (ddl_conv1_wgrad(x, e->dfull[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
+  DDL_CHECK_CUDA(cudaEventRecord(e->ev_join, w));
+  DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join, 0));
   return 0;
 }
 
@@ -322,7 +349,7 @@ const float* ddl_engine_buffer(const DdlEngine* e, int which) {
   if (which == 6) return e->dh1;
   if (which == 7) return e->dh2;
   if (which >= 8 && which < 12) return e->dpool[which - 8];
-  if (which == 12) return e->dfull;
+  if (which == 12) return e->dfull[0];
   if (which == 13) return e->raw;
   return nullptr;
 }

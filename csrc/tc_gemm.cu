@@ -67,6 +67,8 @@ struct WgradParams {
   int ksize;
   int ca, cb;                      // channels of the gradient operand (M side) and of the input operand (N side)
   int mtiles, ntiles, ntile;
+  int tpc, tgroups;                // filter taps handled by one CTA (concatenated along the MMA N dimension)
+  int a_alloc;                     // A boxes that own shared memory (>= live boxes)
   int psplit;
   int stages;
   float* out;                      // [taps][cb][ca], accumulated with red.add
@@ -271,7 +273,13 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
 
 // ------------------------------------------------------------------------------------------------
 // wgrad: out[tap][b][a] += sum_{pix} G[pix, a] * X[pix + off(tap), b]
-// grid = (taps, mtiles * ntiles, psplit)
+// grid = (tap groups, mtiles * ntiles, psplit)
+//
+// Both operands are MN-major (the reduction runs over pixels).  An MN-major B operand is a row of
+// 32-column atoms one LBO apart - so the shifted X boxes of SEVERAL taps, laid out back to back, are
+// one wide B operand: a single N <= 256 MMA multiplies the dY tile with up to 256/Cin taps at once and
+// drops tap t into TMEM columns [t*ntile, (t+1)*ntile).  dY is fetched once per pixel tile for all of
+// them (vs once per tap), and the MMA count falls by the same factor.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreadsTc, 1)
 tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_x,
@@ -280,23 +288,25 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int R = p.bw * p.bh * p.bn;
   const int box_bytes = R * 128;
-  const int a_boxes = kTileM / 32, b_boxes = p.ntile / 32;
-  const int stage_bytes = (a_boxes + b_boxes) * box_bytes;
+  const int b_boxes = p.ntile / 32;                       // atoms per tap
+  const int stage_bytes = (p.a_alloc + p.tpc * b_boxes) * box_bytes;
   PipeBars* bars = (PipeBars*)(smem + (size_t)p.stages * stage_bytes);
 
   const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
-  const int tap = blockIdx.x;
+  const int taps = p.ksize * p.ksize;
+  const int tap0 = blockIdx.x * p.tpc;
+  const int ntap = min(p.tpc, taps - tap0);
   const int mt = blockIdx.y % p.mtiles, nt = blockIdx.y / p.mtiles;
   const int a0 = mt * kTileM, b0 = nt * p.ntile;
   const int half = p.ksize / 2;
-  const int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
   const int ptiles = p.tiles_w * p.tiles_h * p.tiles_n;
   const int per = (ptiles + p.psplit - 1) / p.psplit;
   const int t_begin = blockIdx.z * per;
   const int t_end = min(ptiles, t_begin + per);
   const int niter = max(0, t_end - t_begin);
-  const uint32_t ncols = tmem_cols_for(p.ntile);
-  const int a_live = min(a_boxes, (p.ca - a0 + 31) / 32);     // boxes that hold real channels
+  const int ctot = ntap * p.ntile;                        // accumulator columns in use
+  const uint32_t ncols = ctot <= 32 ? 32u : ctot <= 64 ? 64u : ctot <= 128 ? 128u : ctot <= 256 ? 256u : 512u;
+  const int a_live = min(kTileM / 32, (p.ca - a0 + 31) / 32);     // boxes that hold real channels
   const int b_live = min(b_boxes, (p.cb - b0 + 31) / 32);
 
   if (threadIdx.x == 0) {
@@ -313,7 +323,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   const uint32_t tmem_base = bars->tmem_addr;
 
   if (warp == 0) {
-    const uint32_t tx = (uint32_t)((a_live + b_live) * box_bytes);
+    const uint32_t tx = (uint32_t)((a_live + ntap * b_live) * box_bytes);
     int s = 0;
     uint32_t ph = 0;
     for (int i = 0; i < niter; ++i) {
@@ -323,20 +333,26 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
         const int tw = t % p.tiles_w, th = (t / p.tiles_w) % p.tiles_h, tn = t / (p.tiles_w * p.tiles_h);
         const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
         uint8_t* sa = smem + (size_t)s * stage_bytes;
-        uint8_t* sb = sa + a_boxes * box_bytes;
+        uint8_t* sb = sa + p.a_alloc * box_bytes;
         mbar_expect_tx(&bars->full[s], tx);
         for (int j = 0; j < a_live; ++j)
           tma_load_4d(sa + j * box_bytes, &map_g, &bars->full[s], a0 + 32 * j, w0, h0, n0);
-        for (int j = 0; j < b_live; ++j)
-          tma_load_4d(sb + j * box_bytes, &map_x, &bars->full[s], b0 + 32 * j, w0 + dw, h0 + dh, n0);
+        for (int tt = 0; tt < ntap; ++tt) {
+          const int tap = tap0 + tt;
+          const int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
+          for (int j = 0; j < b_live; ++j)
+            tma_load_4d(sb + (tt * b_boxes + j) * box_bytes, &map_x, &bars->full[s], b0 + 32 * j, w0 + dw, h0 + dh, n0);
+        }
       }
       __syncwarp();
       if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = umma_idesc_tf32(kTileM, p.ntile, 1, 1);
     const int ksteps = R / kUmmaK;
     const uint32_t smem_base = smem_u32(smem);
+    const int n_first = min(ctot, 256), n_rest = ctot - n_first;       // one or two MMAs per K step
+    const uint32_t idesc0 = umma_idesc_tf32(kTileM, n_first, 1, 1);
+    const uint32_t idesc1 = umma_idesc_tf32(kTileM, n_rest > 0 ? n_rest : 32, 1, 1);
     int s = 0;
     uint32_t ph = 0;
     for (int i = 0; i < niter; ++i) {
@@ -344,11 +360,17 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
       tc_fence_after();
       if (elect_one()) {
         const uint32_t sa = smem_base + (uint32_t)(s * stage_bytes);
-        const uint32_t sb = sa + a_boxes * box_bytes;
+        const uint32_t sb = sa + (uint32_t)(p.a_alloc * box_bytes);
         for (int k = 0; k < ksteps; ++k) {
+          const uint32_t acc = (i > 0 || k > 0) ? 1u : 0u;
           const uint64_t ad = umma_smem_desc(sa + k * 1024, (uint32_t)box_bytes, 512, DDL_UMMA_SW128_BASE32B);
-          const uint64_t bd = umma_smem_desc(sb + k * 1024, (uint32_t)box_bytes, 512, DDL_UMMA_SW128_BASE32B);
-          umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          const uint64_t bd0 = umma_smem_desc(sb + k * 1024, (uint32_t)box_bytes, 512, DDL_UMMA_SW128_BASE32B);
+          umma_tf32(tmem_base, ad, bd0, idesc0, acc);
+          if (n_rest > 0) {
+            const uint64_t bd1 = umma_smem_desc(sb + 8 * box_bytes + k * 1024, (uint32_t)box_bytes, 512,
+                                                DDL_UMMA_SW128_BASE32B);
+            umma_tf32(tmem_base + 256, ad, bd1, idesc1, acc);
+          }
         }
         umma_commit(&bars->empty[s]);
         if (i == niter - 1) umma_commit(&bars->tmem_full);
@@ -362,18 +384,20 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     const int q = warp & 3;
     const int a = a0 + q * 32 + lane;
     const bool valid = a < p.ca && niter > 0;
-    float* obase = p.out + (int64_t)tap * p.cb * p.ca + a;
-    if (lane == 0) mbar_wait(&bars->tmem_full, 0);      // one poller per warp: 128 threads hammering the
-    __syncwarp();                                        // same mbarrier slow the producer / MMA handoffs
+    if (lane == 0) mbar_wait(&bars->tmem_full, 0);
+    __syncwarp();
     tc_fence_after();
-    for (int c0 = 0; c0 < p.ntile; c0 += 16) {
-      float v[16];
-      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-      if (!valid) continue;
+    for (int tt = 0; tt < ntap; ++tt) {
+      float* obase = p.out + (int64_t)(tap0 + tt) * p.cb * p.ca + a;
+      for (int c0 = 0; c0 < p.ntile; c0 += 16) {
+        float v[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tt * p.ntile + c0), v);
+        if (!valid) continue;
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int b = b0 + c0 + j;
-        if (b < p.cb) atomicAdd(obase + (int64_t)b * p.ca, v[j]);
+        for (int j = 0; j < 16; ++j) {
+          const int bcol = b0 + c0 + j;
+          if (bcol < p.cb) atomicAdd(obase + (int64_t)bcol * p.ca, v[j]);
+        }
       }
     }
   }
@@ -538,27 +562,44 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   pl->kind = 1;
   WgradParams& p = pl->wg;
   p.N = N; p.H = H; p.W = W;
-  // rows per stage: multiple of 8 (one UMMA K step = 8 pixel rows); cap so 2+ stages fit in smem
-  const int boxes = kTileM / 32 + ntile / 32;
-  int max_rows = ((200 * 1024 / 2) / (boxes * 128)) & ~7;
+  const int taps = ksize * ksize;
+  const int b_boxes = ntile / 32;
+  p.ksize = ksize; p.ca = ca; p.cb = cb;
+  p.mtiles = ceil_div(ca, kTileM); p.ntile = ntile; p.ntiles = ceil_div(cb, ntile);
+  // taps per CTA: up to 512 accumulator columns (two N <= 256 MMAs per K step), balanced over the groups;
+  // the second MMA's B descriptor starts 8 atoms in, so a group wider than 256 columns needs ntile | 256
+  int tpc_max = 512 / ntile;
+  if (tpc_max > 1 && (256 % ntile) != 0) tpc_max = 256 / ntile > 0 ? 256 / ntile : 1;
+  if (tpc_max < 1) tpc_max = 1;
+  if (getenv("DDL_WGRAD_TPC")) tpc_max = atoi(getenv("DDL_WGRAD_TPC"));
+  if (tpc_max > taps) tpc_max = taps;
+  p.tgroups = ceil_div(taps, tpc_max);
+  p.tpc = ceil_div(taps, p.tgroups);
+  const int a_live_max = ca >= kTileM ? kTileM / 32 : ceil_div(ca, 32);
+  p.a_alloc = a_live_max;
+  if (p.a_alloc + p.tpc * b_boxes < kTileM / 32) p.a_alloc = kTileM / 32;   // the M=128 descriptor spans 4 atoms
+  const int boxes = p.a_alloc + p.tpc * b_boxes;
+  // rows per stage: multiple of 8 (one UMMA K step = 8 pixel rows); two stages must fit in shared memory
+  int max_rows = ((216 * 1024 / 2) / (boxes * 128)) & ~7;
   if (max_rows > 128) max_rows = 128;
+  if (max_rows < 8) { delete pl; return fail("tap group does not fit in shared memory"); }
   choose_box(N, H, W, max_rows, 8, &p.bw, &p.bh, &p.bn);
   const int R = p.bw * p.bh * p.bn;
   if (R % 8) { delete pl; return fail("no pixel box with a multiple of 8 rows"); }
   if (p.bw > 256 || p.bh > 256 || p.bn > 256 || R > 256) { delete pl; return fail("pixel box does not fit TMA limits"); }
   p.tiles_w = ceil_div(W, p.bw); p.tiles_h = ceil_div(H, p.bh); p.tiles_n = ceil_div(N, p.bn);
-  p.ksize = ksize; p.ca = ca; p.cb = cb;
-  p.mtiles = ceil_div(ca, kTileM); p.ntile = ntile; p.ntiles = ceil_div(cb, ntile);
   const int ptiles = p.tiles_w * p.tiles_h * p.tiles_n;
+  if (psplit <= 0) psplit = ceil_div(148, p.tgroups * p.mtiles * p.ntiles);   // auto: about one wave of CTAs
   p.psplit = psplit < 1 ? 1 : (psplit > ptiles ? ptiles : psplit);
   const int stage_bytes = boxes * R * 128;
-  int stages = (200 * 1024) / stage_bytes;           // wgrad grids are <= ~150 CTAs: one fat CTA per SM
+  int stages = (216 * 1024) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
+  if (stages > ceil_div(ptiles, p.psplit)) stages = ceil_div(ptiles, p.psplit) < 2 ? 2 : ceil_div(ptiles, p.psplit);
   if (stages < 1) { delete pl; return fail("stage does not fit in shared memory"); }
   p.stages = stages;
   p.out = out;
   pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
-  pl->grid = dim3(ksize * ksize, p.mtiles * p.ntiles, p.psplit);
+  pl->grid = dim3(p.tgroups, p.mtiles * p.ntiles, p.psplit);
   const uint64_t dg[4] = {(uint64_t)ca, (uint64_t)W, (uint64_t)H, (uint64_t)N};
   const uint64_t dx[4] = {(uint64_t)cb, (uint64_t)W, (uint64_t)H, (uint64_t)N};
   const uint32_t bx[4] = {32, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};

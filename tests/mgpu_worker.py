@@ -26,42 +26,60 @@ def base_cfg(**kw):
     return Config(**d).validate()
 
 
-def case_sync(rank, world, layout_kind, shard, graphs):
+def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd"):
+    """Training loop through the engine: every worker holds bitwise-identical parameters after each
+    sync step, owners' ranges are the source of truth, the CUDA-graph path is taken."""
+    P = world if layout_kind == "colocated" else 1
+    W = world if layout_kind == "colocated" else world - 1
+    cfg = base_cfg(mode="sync", shard=shard if P > 1 else "none", num_ps=P, num_workers=W, transport="fused",
+                   graphs=graphs, variant="mnist_sync_sharding_greedy", optimizer=opt)
+    tr = SPMDTrainer(cfg, rank, world, rank, layout_kind)
+    nb = 5
+    for i in range(nb):
+        tr.train_step(i)
+        torch.cuda.synchronize()
+        allp = gather_flat(tr.params.flat.clone())
+        wr = tr.layout.worker_ranks
+        for r in wr[1:]:
+            assert torch.equal(allp[wr[0]], allp[r]), "step %d: worker %d differs from worker %d" % (i, r, wr[0])
+        for sh in range(P):
+            b, e = tr.plan.shard_range[sh]
+            assert torch.equal(allp[tr.layout.owner_rank(sh)][b:e], allp[wr[0]][b:e]), "owner range mismatch"
+    st = tr.transport.stats()
+    assert st["optimizer_steps"] == nb, st
+    if graphs and tr.layout.is_worker:
+        assert tr._graph is not None, "CUDA graph path was not taken"
+    tr.transport.close()
+    dist.barrier()
+
+
+def case_sync_vs_nccl(rank, world, layout_kind, shard, opt):
+    """The fused K1+K3 kernel against reduce + optimizer + broadcast done with NCCL, on IDENTICAL
+    gradients (the engine's red.add-ordered sums are not run-to-run reproducible, and a ULP can flip a
+    ReLU / pool arg-max, so end-to-end training runs are only statistically comparable)."""
     P = world if layout_kind == "colocated" else 1
     W = world if layout_kind == "colocated" else world - 1
     results = {}
     for transport in ("fused", "nccl"):
         cfg = base_cfg(mode="sync", shard=shard if P > 1 else "none", num_ps=P, num_workers=W, transport=transport,
-                       graphs=graphs, variant="mnist_sync_sharding_greedy")
+                       variant="mnist_sync_sharding_greedy", optimizer=opt, lr=0.01, reduce="mean", graphs=False)
         tr = SPMDTrainer(cfg, rank, world, rank, layout_kind)
-        nb = 5
-        for i in range(nb):
-            tr.train_step(i)
-        torch.cuda.synchronize()
-        dist.barrier()
-        flat = tr.params.flat.clone()
-        if tr.layout.is_worker:
-            results[transport] = flat
-        # (a) every worker holds bitwise-identical parameters after a sync step
-        allp = gather_flat(flat)
-        wr = tr.layout.worker_ranks
-        for r in wr[1:]:
-            assert torch.equal(allp[wr[0]], allp[r]), "%s: worker %d differs from worker %d" % (transport, r, wr[0])
-        # owners' ranges are the source of truth
-        for sh in range(P):
-            b, e = tr.plan.shard_range[sh]
-            assert torch.equal(allp[tr.layout.owner_rank(sh)][b:e], allp[wr[0]][b:e]), "owner range mismatch"
-        st = tr.transport.stats() if hasattr(tr.transport, "stats") else {}
-        if transport == "fused":
-            assert st["optimizer_steps"] == nb, st
-            if graphs and tr.layout.is_worker:
-                assert tr._graph is not None, "CUDA graph path was not taken"
+        for k in range(3):
+            gen = torch.Generator(device="cuda").manual_seed(100 * k + rank)
+            tr.grads.flat.copy_(torch.randn(tr.grads.flat.shape, device="cuda", generator=gen))
+            if not tr.layout.is_worker:
+                tr.grads.flat.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            tr.transport.begin_step()
+            tr.transport.step()
+            torch.cuda.synchronize()
+            dist.barrier()
+        results[transport] = tr.params.flat.clone()
         tr.transport.close()
-    # (b) the fused kernel equals reduce + optimizer + broadcast done with NCCL (same engine gradients;
-    #     only the fp32 summation order differs)
-    if "fused" in results and "nccl" in results:
+    if rank in tr.layout.worker_ranks:
         diff = (results["fused"] - results["nccl"]).abs().max().item()
-        assert diff < 5e-5, "fused vs nccl parameter difference %g" % diff
+        assert diff < 2e-6, "fused vs nccl parameter difference %g (%s, %s)" % (diff, shard, opt)
     dist.barrier()
 
 
@@ -109,7 +127,7 @@ def case_async_train(rank, world):
     stats = tr.run()
     assert stats["transport_stats"]["pushes_received"] == 6 * world, stats
     assert 0.0 <= stats["final_accuracy"] <= 1.0
-    tr.close()
+    tr.transport.close()
 
 
 def main():
@@ -119,9 +137,13 @@ def main():
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     if case == "sync_colocated":
         case_sync(rank, world, "colocated", "greedy", graphs=False)
-        case_sync(rank, world, "colocated", "flat", graphs=True)
+        case_sync(rank, world, "colocated", "flat", graphs=True, opt="adam")
     elif case == "sync_dedicated":
-        case_sync(rank, world, "dedicated", "none", graphs=True)
+        case_sync(rank, world, "dedicated", "none", graphs=True, opt="adam")
+    elif case == "sync_vs_nccl":
+        case_sync_vs_nccl(rank, world, "colocated", "greedy", "adam")
+        case_sync_vs_nccl(rank, world, "colocated", "flat", "momentum")
+        case_sync_vs_nccl(rank, world, "dedicated", "none", "sgd")
     elif case == "async_sgd":
         case_async_counting(rank, world, "sgd")
     elif case == "async_adam":
