@@ -157,14 +157,7 @@ int build_bwd(DdlEngine* e) {
   for (int l = 1; l < e->nconv; ++l, v += 2) {
     const int S = e->S[l], cin = e->C[l], cout = e->C[l + 1];
     const int nt_w = cin >= 128 ? 128 : (cin >= 64 ? 64 : 32);
-    DdlTcPlan* probe = ddl_tc_plan_wgrad(e->dfull[l], e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, 1);
-    if (!probe) return -1;
-    int info[8];
-    ddl_tc_plan_info(probe, info);
-    ddl_tc_plan_destroy(probe);
-    int base = info[0] * info[1];
-    int psplit = base >= 120 ? 1 : cdiv(148, base);
-    e->wg_conv[l - 1] = ddl_tc_plan_wgrad(e->dfull[l], e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, psplit);
+    e->wg_conv[l - 1] = ddl_tc_plan_wgrad(e->dfull[l], e->pooled[l - 1], e->G(v), B, S, S, cout, cin, 5, nt_w, 0);
     if (!e->wg_conv[l - 1]) return -1;
     // dgrad: dp_{l-1}[pix, cin] = sum_{tap, cout} dY[pix - off, cout] * W[tap][cin][cout]
     DdlTcPlan* probe2 = ddl_tc_plan_act(1, e->dfull[l], e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, 32, 1, 0,

@@ -84,6 +84,18 @@ struct alignas(8) PipeBars {
   uint32_t pad;
 };
 
+// 4x4 transpose across a quad of lanes (two butterfly rounds, 4 shuffles): in r[c] = (this lane, column c),
+// out r[k] = (quad lane k, column ql).
+__device__ __forceinline__ void quad_transpose4(float r[4], int ql) {
+  const bool b0 = ql & 1, b1 = ql & 2;
+  float sx = b0 ? r[0] : r[1], sy = b0 ? r[2] : r[3];
+  float rx = __shfl_xor_sync(0xffffffffu, sx, 1), ry = __shfl_xor_sync(0xffffffffu, sy, 1);
+  if (b0) { r[0] = rx; r[2] = ry; } else { r[1] = rx; r[3] = ry; }
+  sx = b1 ? r[0] : r[2]; sy = b1 ? r[1] : r[3];
+  rx = __shfl_xor_sync(0xffffffffu, sx, 2); ry = __shfl_xor_sync(0xffffffffu, sy, 2);
+  if (b1) { r[0] = rx; r[1] = ry; } else { r[2] = rx; r[3] = ry; }
+}
+
 __device__ __forceinline__ uint32_t tmem_cols_for(int n) {
   return n <= 32 ? 32u : n <= 64 ? 64u : n <= 128 ? 128u : 256u;
 }
@@ -387,16 +399,34 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     if (lane == 0) mbar_wait(&bars->tmem_full, 0);
     __syncwarp();
     tc_fence_after();
+    // out[tap][b][a]: `a` (this lane's TMEM row) is the contiguous index.  A 4x4 register transpose inside
+    // each quad of lanes turns 16 scalar reds per lane into 4 x red.global.add.v4.f32 on 4 consecutive a.
+    const int ql = lane & 3;
+    const int aq = a0 + q * 32 + (lane & ~3);               // first a of this quad
+    const bool vec_ok = (p.ca % 4) == 0;
     for (int tt = 0; tt < ntap; ++tt) {
-      float* obase = p.out + (int64_t)(tap0 + tt) * p.cb * p.ca + a;
+      float* otap = p.out + (int64_t)(tap0 + tt) * p.cb * p.ca;
       for (int c0 = 0; c0 < p.ntile; c0 += 16) {
         float v[16];
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(tt * p.ntile + c0), v);
-        if (!valid) continue;
+        if (niter == 0) continue;
+        if (!vec_ok) {
+          if (a < p.ca) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int bcol = b0 + c0 + j;
-          if (bcol < p.cb) atomicAdd(obase + (int64_t)bcol * p.ca, v[j]);
+            for (int j = 0; j < 16; ++j) {
+              const int bcol = b0 + c0 + j;
+              if (bcol < p.cb) atomicAdd(otap + (int64_t)bcol * p.ca + a, v[j]);
+            }
+          }
+          continue;
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {                       // registers 4g..4g+3 <-> columns b = c0+4g..+3
+          float r[4] = {v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]};
+          quad_transpose4(r, ql);                           // r[k] = value of quad lane k for column 4g + ql
+          const int bcol = b0 + c0 + 4 * g + ql;
+          if (bcol < p.cb && aq < p.ca)
+            red_add_v4_f32(otap + (int64_t)bcol * p.ca + aq, make_float4(r[0], r[1], r[2], r[3]));
         }
       }
     }
@@ -589,7 +619,13 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   if (p.bw > 256 || p.bh > 256 || p.bn > 256 || R > 256) { delete pl; return fail("pixel box does not fit TMA limits"); }
   p.tiles_w = ceil_div(W, p.bw); p.tiles_h = ceil_div(H, p.bh); p.tiles_n = ceil_div(N, p.bn);
   const int ptiles = p.tiles_w * p.tiles_h * p.tiles_n;
-  if (psplit <= 0) psplit = ceil_div(148, p.tgroups * p.mtiles * p.ntiles);   // auto: about one wave of CTAs
+  if (psplit <= 0) {
+    // Every pixel split re-adds the whole dW tile with red.add, so splits are not free: aim for >= ~12
+    // pixel tiles per CTA and never more than one wave of CTAs.
+    const int wave = ceil_div(148, p.tgroups * p.mtiles * p.ntiles);
+    psplit = ceil_div(ptiles, 12);
+    if (psplit > wave) psplit = wave;
+  }
   p.psplit = psplit < 1 ? 1 : (psplit > ptiles ? ptiles : psplit);
   const int stage_bytes = boxes * R * 128;
   int stages = (216 * 1024) / stage_bytes;
