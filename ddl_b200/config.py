@@ -19,7 +19,7 @@ from dataclasses import dataclass, field
 from typing import Optional, Sequence
 
 SHARD_MODES = ("none", "block", "round_robin", "greedy", "greedy_interleave", "flat")
-TRANSPORTS = ("auto", "fused", "nccl", "host")
+TRANSPORTS = ("auto", "fused", "nccl", "host", "local")
 OPTIMIZERS = ("adam", "sgd", "momentum")
 REDUCES = ("sum", "mean")
 BACKENDS = ("auto", "native", "torch")

@@ -59,8 +59,8 @@ def resolve_transport(cfg: Config, device: torch.device, world: int) -> str:
         return "local" if world == 1 else "nccl"
     if t == "fused" and device.type != "cuda":
         raise RuntimeError("the fused transport needs CUDA peer memory; use --transport nccl/host on CPU")
-    if world == 1 and t in ("nccl", "fused") and device.type != "cuda":
-        return "local"
+    if world == 1 and (t == "nccl" or (t == "fused" and device.type != "cuda")):
+        return "local"                  # one process: the collective rung degenerates to the local optimizer
     return t
 
 
