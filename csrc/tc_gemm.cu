@@ -666,6 +666,118 @@ int ddl_tc_plan_trace(const DdlTcPlan* pl, unsigned long long* host_out, int n) 
   return 0;
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Allocation-free convolution block (no counterpart in the reference).
+ *
+ * Who this is for: a host program that must not call cudaMalloc.  Two kinds exist in practice.  Some
+ * have handed the whole device to another allocator - a framework's caching pool told to own all free
+ * memory, or an MPS / MIG slice with a hard quota - so one more cudaMalloc simply fails.  Others run a
+ * latency-critical loop (serving, control) and cannot accept cudaMalloc's device-wide synchronisation
+ * and unbounded latency in the middle of it.  Every other conv entry point of this library needs the
+ * caller to provide (hence allocate) a buffer for the raw convolution sums; this one keeps that buffer
+ * inside the library, in the file-scope array below, which every GPU that loads the library holds until
+ * the process exits.  The caller passes only inputs and outputs.
+ *
+ * y[N, ceil(H/2), ceil(W/2), cout] = maxpool2x2_SAME(relu(conv5x5_SAME(x, w) + bias)),  idx optional.
+ *
+ * Rules:
+ *  - the raw sums (N*H*W*cout floats) must fit DDL_STATIC_SCRATCH_BYTES, else the call is refused;
+ *  - the first call on each device performs a one-time set-up (symbol address lookup, kernel attribute);
+ *    make that first call before starting any stream capture;
+ *  - all calls share the one array, which keeps the previous call's contents; this function clears the
+ *    part it accumulates into, and two calls that overlap on the GPU (any streams) race on it - serialise
+ *    them;
+ *  - it calls no cudaMalloc / cudaFree and no allocating library routine.
+ */
+static __device__ __align__(256) float g_static_scratch[DDL_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mutex;
+float* g_static_ptr[kMaxDevices] = {};       // device address of g_static_scratch, per device
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: handing it to a
+// kernel would fault (or, where the GPU can reach host memory, quietly use the wrong bytes).  The real
+// address comes from cudaGetSymbolAddress, once per device, with that device current.
+int static_scratch_setup(float** out) {
+  int dev = -1;
+  DDL_CHECK_CUDA(cudaGetDevice(&dev));
+  DDL_REQUIRE(dev >= 0 && dev < kMaxDevices, "device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    DDL_CHECK_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    DDL_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    DDL_CHECK_CUDA(cudaFuncSetAttribute(tc_act_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    g_static_ptr[dev] = (float*)p;
+  }
+  *out = g_static_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bias, float* y, uint8_t* idx,
+                                 int N, int H, int W, int cin, int cout, cudaStream_t s) {
+  DDL_REQUIRE(N > 0 && H > 0 && W > 0 && cin > 0 && cout > 0, "ddl_conv5x5_relu_pool_static: empty shape");
+  DDL_REQUIRE(cin % 4 == 0 && cout % 32 == 0, "ddl_conv5x5_relu_pool_static: cin %% 4 == 0 and cout %% 32 == 0 required");
+  const size_t need = (size_t)N * H * W * cout * sizeof(float);
+  DDL_REQUIRE(need <= (size_t)DDL_STATIC_SCRATCH_BYTES,
+              "ddl_conv5x5_relu_pool_static: N*H*W*cout*4 = %zu bytes exceeds the built-in scratch of %d bytes "
+              "(DDL_STATIC_SCRATCH_BYTES); use ddl_tc_plan_act with your own buffer instead",
+              need, (int)DDL_STATIC_SCRATCH_BYTES);
+  float* raw = nullptr;
+  if (static_scratch_setup(&raw)) return -1;
+
+  // a plan on the stack: same geometry rules as ddl_tc_plan_act(dgrad = 0), nothing heap-allocated
+  DdlTcPlan pl;
+  pl.kind = 0;
+  ActParams& p = pl.act;
+  p = ActParams();
+  p.N = N; p.H = H; p.W = W;
+  choose_box(N, H, W, kTileM, 1, &p.bw, &p.bh, &p.bn);
+  p.tiles_w = ceil_div(W, p.bw); p.tiles_h = ceil_div(H, p.bh); p.tiles_n = ceil_div(N, p.bn);
+  p.ksize = 5; p.flip = 0;
+  p.cblocks = ceil_div(cin, kKB);
+  p.kiters = 25 * p.cblocks;
+  int ntile = 32;
+  for (int c : {256, 128, 64, 32}) if (cout % c == 0) { ntile = c; break; }
+  const int ctas = p.tiles_w * p.tiles_h * p.tiles_n * (cout / ntile);
+  int ksplit = 1;
+  if (ctas < 100) {
+    ksplit = (140 + ctas / 2) / ctas;
+    if (ksplit > p.kiters / 4) ksplit = p.kiters / 4 > 0 ? p.kiters / 4 : 1;
+    if (ksplit > 16) ksplit = 16;
+  }
+  p.ksplit = ksplit;
+  p.nout = cout; p.ntile = ntile;
+  p.b_mn_major = 1;
+  p.flags = ksplit > 1 ? EPI_ATOMIC : 0;
+  p.debug = 0; p.trace = nullptr;
+  p.out = raw; p.bias = nullptr; p.colsum = nullptr; p.mask_act = nullptr; p.mask_scale = 1.f;
+  p.st = nullptr; p.drop_stream_off = 0; p.drop_thresh24 = 1u << 24; p.drop_inv_keep = 1.f;
+  const int stage_bytes = kTileM * 128 + ntile * 128;
+  int stages = (110 * 1024) / stage_bytes;
+  if (stages < 2) stages = 2;
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages > p.kiters) stages = p.kiters < 2 ? 2 : p.kiters;
+  p.stages = stages;
+  pl.smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
+  pl.grid = dim3(p.tiles_w * p.tiles_h * p.tiles_n, cout / ntile, ksplit);
+  const uint64_t da[4] = {(uint64_t)cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  const uint32_t ba[4] = {kKB, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
+  if (make_map4(&pl.map_a, x, da, ba, false)) return -1;
+  const uint64_t dw[4] = {(uint64_t)cout, (uint64_t)cin, 25, 1};
+  const uint32_t bwb[4] = {32, kKB, 1, 1};
+  if (make_map4(&pl.map_b, w, dw, bwb, true)) return -1;
+
+  // split-K partial sums are added with red.add, so the region must start at zero; the array still
+  // holds whatever the previous call left there
+  if (ksplit > 1) DDL_CHECK_CUDA(cudaMemsetAsync(raw, 0, need, s));
+  tc_act_gemm_kernel<<<pl.grid, kThreadsTc, pl.smem, s>>>(pl.map_a, pl.map_b, pl.act);
+  DDL_LAUNCH_CHECK();
+  return ddl_maxpool_fwd(raw, bias, y, idx, N, H, W, cout, s);
+}
+
 /* introspection for tests / profiling notes: fills {grid.x, grid.y, grid.z, stages, smem, bw, bh, bn} */
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8) {
   DDL_REQUIRE(pl != nullptr, "ddl_tc_plan_info: null plan");

@@ -96,6 +96,21 @@ int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);
 void ddl_tc_plan_destroy(DdlTcPlan* pl);
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8);
 
+/* ---- allocation-free convolution block (csrc/tc_gemm.cu).  No counterpart in the reference. --------
+ * For host programs that must not call cudaMalloc: ones that have given the whole device to another
+ * allocator (a caching pool that owns all free memory, an MPS / MIG slice with a hard quota), where a
+ * further cudaMalloc fails, and latency-critical loops that cannot take cudaMalloc's device-wide
+ * synchronisation.  y = maxpool2x2_SAME(relu(conv5x5_SAME(x, w) + bias)); x [N,H,W,cin], w [5,5,cin,cout],
+ * y [N,ceil(H/2),ceil(W/2),cout], idx (may be NULL) the pool arg-max bytes.  The raw convolution sums live
+ * in an array built into the library (DDL_STATIC_SCRATCH_BYTES on every GPU that loads it, held until
+ * exit): N*H*W*cout*4 bytes must fit or the call is refused with an error naming the limit.  The first
+ * call on a device does a one-time set-up and should be made before any stream capture starts.  All calls
+ * share that array (it keeps the last call's contents; this function zeroes what it accumulates into), so
+ * calls that overlap on the GPU race - serialise them.  Calls no cudaMalloc / cudaFree / allocating routine. */
+#define DDL_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bias, float* y, uint8_t* idx,
+                                 int N, int H, int W, int cin, int cout, cudaStream_t s);
+
 /* ---- peer-memory communication (csrc/comm.cu) -----------------------------------------------
  * Replaces the reference's mpi4py layer (SURVEY 2.3 call-site table). */
 #define DDL_MAX_SKIP 4
