@@ -89,6 +89,7 @@ def parse():
     ap.add_argument("--optimizer", default="adam")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--no-k4", action="store_true", help="disable the pull fused into the fc1/fc2 GEMMs")
     return ap.parse_args()
 
 
@@ -131,7 +132,8 @@ def main() -> int:
     cfg = Config(variant=a.variant, mode=mode, shard=shard, num_ps=num_ps, num_workers=world,
                  batch_size=a.batch_size, optimizer=a.optimizer, transport=transport, backend=backend,
                  synthetic=True, synthetic_train=max(6000, a.batch_size * 32), synthetic_test=1000, seed=1234,
-                 eval_every=0, width_mult=a.width_mult, graphs=not a.no_graphs, log_time=False).validate()
+                 eval_every=0, width_mult=a.width_mult, graphs=not a.no_graphs, log_time=False,
+                 fused_pull_gemm=not a.no_k4).validate()
     kind = "colocated" if world > 1 else "auto"
     if world > 1 and num_ps == 1:
         kind = "colocated"
@@ -224,7 +226,8 @@ def main() -> int:
                        "parallelism": "ps%d+w%d colocated, %s transport" % (num_ps, world, tr.transport.name),
                        "optimizer": a.optimizer, "keep_prob": cfg.keep_prob,
                        "l2": "256 MiB written between timed steps" if flush is not None else "not flushed",
-                       "cuda_graph": graph_mode, "backend": backend},
+                       "cuda_graph": graph_mode, "backend": backend,
+                       "k4_fused_pull_gemm": bool(getattr(tr.transport, "k4_src", None))},
             "clocks": clocks,
             "e2e": {"value": total / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": e2e_s * 1e3 / a.steps},

@@ -111,13 +111,13 @@ int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
     const int S = e->S[l], cin = e->C[l], cout = e->C[l + 1];
     // probe the pixel tiling with a throw-away plan to size ntile / ksplit
     DdlTcPlan* probe = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, 32, 1, 0,
-                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
+                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!probe) return -1;
     int nt, ks;
     pick_tiling(pix_tiles_of(probe), cout, 25 * cdiv(cin, 32), true, &nt, &ks);
     ddl_tc_plan_destroy(probe);
     out->conv[l - 1] = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, nt, ks, 0,
-                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
+                                       nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!out->conv[l - 1]) return -1;
     out->conv_split[l - 1] = ks;
   }
@@ -126,12 +126,12 @@ int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
   const float kp = train ? c.keep_prob : 1.f;
   const int drop = (train && c.keep_prob < 1.f) ? 4 : 0;
   if (e->nconv) {
-    out->fc[0] = ddl_tc_plan_act(0, fc_in, e->P(vf), e->h1, B, 1, 1, e->F[0], e->F[1], 1, 32, 1, 1 | 2 | drop,
-                                 e->P(vf + 1), nullptr, 1.f, train ? c.st : nullptr, 0, kp, nullptr);
+    out->fc[0] = ddl_tc_plan_act(0, fc_in, (train && c.fc_w_src[0]) ? c.fc_w_src[0] : e->P(vf), e->h1, B, 1, 1, e->F[0], e->F[1], 1, 32, 1, 1 | 2 | drop,
+                                 e->P(vf + 1), nullptr, 1.f, train ? c.st : nullptr, 0, kp, nullptr, train && c.fc_w_src[0] ? const_cast<float*>(e->P(vf)) : nullptr);
     if (!out->fc[0]) return -1;
   }
-  out->fc[1] = ddl_tc_plan_act(0, e->h1, e->P(vf + 2), e->h2, B, 1, 1, e->F[1], e->F[2], 1, 32, 1, 1 | drop,
-                               e->P(vf + 3), nullptr, 1.f, train ? c.st : nullptr, 1, kp, nullptr);
+  out->fc[1] = ddl_tc_plan_act(0, e->h1, (train && c.fc_w_src[1]) ? c.fc_w_src[1] : e->P(vf + 2), e->h2, B, 1, 1, e->F[1], e->F[2], 1, 32, 1, 1 | drop,
+                               e->P(vf + 3), nullptr, 1.f, train ? c.st : nullptr, 1, kp, nullptr, train && c.fc_w_src[1] ? const_cast<float*>(e->P(vf + 2)) : nullptr);
   if (!out->fc[1]) return -1;
   return 0;
 }
@@ -145,12 +145,12 @@ int build_bwd(DdlEngine* e) {
   e->wg_fc[1] = ddl_tc_plan_wgrad(e->dh2, e->h1, e->G(vf + 2), B, 1, 1, e->F[2], e->F[1], 1, 64, 1);
   // its epilogue also reduces the columns of dh1 into the fc1 bias gradient
   e->dg_fc[1] = ddl_tc_plan_act(1, e->dh2, e->P(vf + 2), e->dh1, B, 1, 1, e->F[2], e->F[1], 1, 32, 1, 8, nullptr,
-                                e->h1, inv_keep, nullptr, 0, 1.f, e->G(vf + 1));
+                                e->h1, inv_keep, nullptr, 0, 1.f, e->G(vf + 1), nullptr);
   if (!e->wg_fc[1] || !e->dg_fc[1]) return -1;
   if (e->nconv) {
     e->wg_fc[0] = ddl_tc_plan_wgrad(e->dh1, e->pooled[3], e->G(vf), B, 1, 1, e->F[1], e->F[0], 1, 64, 1);
     e->dg_fc[0] = ddl_tc_plan_act(1, e->dh1, e->P(vf), e->dpool[3], B, 1, 1, e->F[1], e->F[0], 1, 32, 1, 0, nullptr,
-                                  nullptr, 1.f, nullptr, 0, 1.f, nullptr);
+                                  nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!e->wg_fc[0] || !e->dg_fc[0]) return -1;
   }
   int v = 2;
@@ -161,13 +161,13 @@ int build_bwd(DdlEngine* e) {
     if (!e->wg_conv[l - 1]) return -1;
     // dgrad: dp_{l-1}[pix, cin] = sum_{tap, cout} dY[pix - off, cout] * W[tap][cin][cout]
     DdlTcPlan* probe2 = ddl_tc_plan_act(1, e->dfull[l], e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, 32, 1, 0,
-                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
+                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!probe2) return -1;
     int nt, ks;
     pick_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), true, &nt, &ks);
     ddl_tc_plan_destroy(probe2);
     e->dg_conv[l - 1] = ddl_tc_plan_act(1, e->dfull[l], e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, nt, ks, 0,
-                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr);
+                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!e->dg_conv[l - 1]) return -1;
     e->dg_split[l - 1] = ks;
   }

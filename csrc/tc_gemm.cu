@@ -47,6 +47,8 @@ struct ActParams {
   int stages;
   int b_mn_major;                  // 1: weights [tap][cred][nout] (fprop), 0: [tap][nout][cred] (dgrad)
   int flags;
+  int pull;                        // K4: weight tiles come from another rank's arena (map_w on a peer pointer);
+                                   // pixel-tile 0 CTAs write every tile through to the local arena (map_wst)
   int debug;                       // perf experiments only: 1 = skip MMA issue, 2 = skip TMA loads
   unsigned long long* trace;       // perf experiments only: per-iteration clock64 stamps of CTA (0,0,0)
   float* out;                      // [N*H*W, nout]
@@ -106,7 +108,7 @@ __device__ __forceinline__ uint32_t tmem_cols_for(int n) {
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreadsTc, 1)
 tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_w,
-                   const ActParams p) {
+                   const __grid_constant__ CUtensorMap map_wst, const ActParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int a_bytes = kTileM * 128;
@@ -125,18 +127,47 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const int niter = max(0, k_end - k_begin);
   const uint32_t ncols = tmem_cols_for(p.ntile);
 
+  // K4 write-through: one CTA per weight tile (the first pixel tile) persists what it pulled
+  const bool store_through = p.pull && blockIdx.x == 0 && p.b_mn_major;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < p.stages; ++s) { mbar_init(&bars->full[s], 1); mbar_init(&bars->empty[s], 1); }
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&bars->full[s], 1);
+      mbar_init(&bars->empty[s], store_through ? 2 : 1);      // MMA commit (+ the store warp's arrive)
+    }
     mbar_init(&bars->tmem_full, 1);
     fence_barrier_init();
     tma_prefetch_desc(&map_act);
     tma_prefetch_desc(&map_w);
+    if (store_through) tma_prefetch_desc(&map_wst);
   }
   if (warp == 1) tmem_alloc(&bars->tmem_addr, ncols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_addr;
+
+  if (warp == 2 && store_through) {
+    // ================= K4 store warp: smem weight tile -> local arena (TMA store), before its epilogue duty
+    int s = 0;
+    uint32_t ph = 0;
+    int tap = k_begin / p.cblocks, cb = k_begin % p.cblocks;
+    for (int i = 0; i < niter; ++i) {
+      mbar_wait(&bars->full[s], ph);
+      if (elect_one()) {
+        uint8_t* sb = smem + (size_t)s * stage_bytes + a_bytes;
+        for (int j = 0; j < p.ntile / 32; ++j)
+          tma_store_4d(&map_wst, sb + j * 4096, nt0 + 32 * j, cb * kKB, tap, 0);
+        tma_store_commit();
+        tma_store_wait_read0();                  // smem may be overwritten once the store has read it
+        mbar_arrive(&bars->empty[s]);
+      }
+      __syncwarp();
+      if (++cb == p.cblocks) { cb = 0; ++tap; }
+      if (++s == p.stages) { s = 0; ph ^= 1u; }
+    }
+    if (elect_one()) tma_store_wait_all0();      // writes complete before the kernel can end
+    __syncwarp();
+  }
 
   if (warp == 0) {
     // ================= TMA producer (warp-uniform loop, one elected lane issues) =================
@@ -507,6 +538,7 @@ void choose_box(int N, int H, int W, int max_rows, int row_mult, int* bw, int* b
 struct DdlTcPlan {
   int kind;                 // 0 act, 1 wgrad
   CUtensorMap map_a, map_b;
+  CUtensorMap map_c;        // act plans with K4 pull: store map of the local weight copy (else = map_b)
   ActParams act;
   WgradParams wg;
   dim3 grid;
@@ -518,7 +550,7 @@ extern "C" {
 DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
                            int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
                            const float* mask_act, float mask_scale, const DdlStepState* st,
-                           uint32_t drop_stream_off, float keep_prob, float* colsum) {
+                           uint32_t drop_stream_off, float keep_prob, float* colsum, float* w_store_dst) {
   auto fail = [](const char* why) -> DdlTcPlan* { ddl::set_error("ddl_tc_plan_act: %s", why); return nullptr; };
   if (cred % 4 || nout % 4) return fail("channel counts must be multiples of 4 (16-byte TMA pitch)");
   if (ntile < 16 || ntile > 256 || ntile % 16) return fail("ntile must be a multiple of 16 in [16, 256]");
@@ -538,6 +570,7 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
   p.nout = nout; p.ntile = ntile;
   p.b_mn_major = dgrad ? 0 : 1;
   p.flags = flags | (p.ksplit > 1 ? EPI_ATOMIC : 0);
+  p.pull = (w_store_dst != nullptr && !dgrad && w_store_dst != w) ? 1 : 0;
   p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
   p.trace = nullptr;
   if (getenv("DDL_TC_TRACE")) {
@@ -570,10 +603,13 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
     const uint64_t dw[4] = {(uint64_t)nout, (uint64_t)cred, (uint64_t)taps, 1};
     const uint32_t bwb[4] = {32, kKB, 1, 1};
     if (make_map4(&pl->map_b, w, dw, bwb, true)) { delete pl; return nullptr; }
+    pl->map_c = pl->map_b;
+    if (p.pull && make_map4(&pl->map_c, w_store_dst, dw, bwb, true)) { delete pl; return nullptr; }
   } else {                // W as [taps][nout][cred]: inner = cred (the reduction)
     const uint64_t dw[4] = {(uint64_t)cred, (uint64_t)nout, (uint64_t)taps, 1};
     const uint32_t bwb[4] = {kKB, (uint32_t)ntile, 1, 1};
     if (make_map4(&pl->map_b, w, dw, bwb, false)) { delete pl; return nullptr; }
+    pl->map_c = pl->map_b;
   }
   if (cudaFuncSetAttribute(tc_act_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) {
     delete pl;
@@ -650,7 +686,7 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s) {
   DDL_REQUIRE(pl != nullptr, "ddl_tc_plan_run: null plan");
   if (pl->kind == 0)
-    tc_act_gemm_kernel<<<pl->grid, kThreadsTc, pl->smem, s>>>(pl->map_a, pl->map_b, pl->act);
+    tc_act_gemm_kernel<<<pl->grid, kThreadsTc, pl->smem, s>>>(pl->map_a, pl->map_b, pl->map_c, pl->act);
   else
     tc_wgrad_kernel<<<pl->grid, kThreadsTc, pl->smem, s>>>(pl->map_a, pl->map_b, pl->wg);
   DDL_LAUNCH_CHECK();
@@ -752,7 +788,7 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
   p.nout = cout; p.ntile = ntile;
   p.b_mn_major = 1;
   p.flags = ksplit > 1 ? EPI_ATOMIC : 0;
-  p.debug = 0; p.trace = nullptr;
+  p.pull = 0; p.debug = 0; p.trace = nullptr;
   p.out = raw; p.bias = nullptr; p.colsum = nullptr; p.mask_act = nullptr; p.mask_scale = 1.f;
   p.st = nullptr; p.drop_stream_off = 0; p.drop_thresh24 = 1u << 24; p.drop_inv_keep = 1.f;
   const int stage_bytes = kTileM * 128 + ntile * 128;
@@ -773,7 +809,7 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
   // split-K partial sums are added with red.add, so the region must start at zero; the array still
   // holds whatever the previous call left there
   if (ksplit > 1) DDL_CHECK_CUDA(cudaMemsetAsync(raw, 0, need, s));
-  tc_act_gemm_kernel<<<pl.grid, kThreadsTc, pl.smem, s>>>(pl.map_a, pl.map_b, pl.act);
+  tc_act_gemm_kernel<<<pl.grid, kThreadsTc, pl.smem, s>>>(pl.map_a, pl.map_b, pl.map_b, pl.act);
   DDL_LAUNCH_CHECK();
   return ddl_maxpool_fwd(raw, bias, y, idx, N, H, W, cout, s);
 }

@@ -71,14 +71,15 @@ class Model:
 
     def __init__(self, spec: ModelSpec, params: Arena, grads: Arena, cfg: Config,
                  max_eval_batch: int = 2000, step_state: Optional[torch.Tensor] = None,
-                 worker: int = 0, num_workers: int = 1):
+                 worker: int = 0, num_workers: int = 1, fc_w_src=None):
         self.spec, self.params, self.grads, self.cfg = spec, params, grads, cfg
         which = pick_backend(cfg, params.device)
         if which == "native":
             if params.device.type != "cuda":
                 raise RuntimeError("the native sm_100a backend needs a CUDA device; use --backend torch on CPU")
             from ..ops.engine import NativeBackend   # raises loudly if the .so is missing
-            self.impl = NativeBackend(spec, params, grads, cfg, max_eval_batch, step_state, worker, num_workers)
+            self.impl = NativeBackend(spec, params, grads, cfg, max_eval_batch, step_state, worker, num_workers,
+                                      fc_w_src)
         else:
             self.impl = TorchBackend(spec, params, grads, cfg)
         self.backend = self.impl.name

@@ -23,7 +23,8 @@ class NativeBackend:
     name = "native"
 
     def __init__(self, spec: ModelSpec, params: Arena, grads: Arena, cfg: Config, max_eval_batch: int = 2000,
-                 step_state: Optional[torch.Tensor] = None, worker: int = 0, num_workers: int = 1):
+                 step_state: Optional[torch.Tensor] = None, worker: int = 0, num_workers: int = 1,
+                 fc_w_src=None):
         if spec.kind != "cnn":
             raise native.NativeError("the native engine implements the CNN; use --backend torch for the MLP")
         self.L = native.lib()
@@ -45,6 +46,9 @@ class NativeBackend:
         for i, off in enumerate(params.plan.var_offset):
             ecfg.var_offset[i] = off
         ecfg.st = self.st.data_ptr()
+        # K4: peer pointers of the fc1 / fc2 weight matrices in their owners' arenas (None = local)
+        for i, v in enumerate((8, 10)):
+            ecfg.fc_w_src[i] = (fc_w_src or {}).get(v)
         self.h = self.L.ddl_engine_create(C.byref(ecfg))
         if not self.h:
             raise native.NativeError("ddl_engine_create: " + native.last_error())

@@ -42,7 +42,7 @@ def conv5x5_fprop(x: torch.Tensor, w: torch.Tensor, ntile: int = 0, ksplit: int 
     out = (torch.zeros if ksplit > 1 else torch.empty)(N, H, W, Cout, device=x.device, dtype=torch.float32)
     nt = ntile or (128 if Cout % 128 == 0 else 64 if Cout % 64 == 0 else 32)
     plan = native.lib().ddl_tc_plan_act(0, native.ptr(x), native.ptr(w), native.ptr(out), N, H, W, Cin, Cout, k, nt,
-                                        ksplit, 0, None, None, 1.0, None, 0, 1.0, None)
+                                        ksplit, 0, None, None, 1.0, None, 0, 1.0, None, None)
     _run_plan(plan)
     return out
 
@@ -54,7 +54,7 @@ def conv5x5_dgrad(dy: torch.Tensor, w: torch.Tensor, ntile: int = 0, ksplit: int
     out = (torch.zeros if ksplit > 1 else torch.empty)(N, H, W, Cin, device=dy.device, dtype=torch.float32)
     nt = ntile or (128 if Cin % 128 == 0 else 64 if Cin % 64 == 0 else 32)
     plan = native.lib().ddl_tc_plan_act(1, native.ptr(dy), native.ptr(w), native.ptr(out), N, H, W, Cout, Cin, k, nt,
-                                        ksplit, 0, None, None, 1.0, None, 0, 1.0, None)
+                                        ksplit, 0, None, None, 1.0, None, 0, 1.0, None, None)
     _run_plan(plan)
     return out
 
@@ -82,7 +82,7 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = 
     flags = (EPI_BIAS if bias is not None else 0) | (EPI_RELU if relu else 0) | (EPI_DROPOUT if dropout else 0)
     st, off, keep = dropout if dropout else (None, 0, 1.0)
     plan = native.lib().ddl_tc_plan_act(0, native.ptr(x), native.ptr(w), native.ptr(out), B, 1, 1, K, N, 1, ntile, 1,
-                                        flags, native.ptr(bias), None, 1.0, native.ptr(st), off, keep, None)
+                                        flags, native.ptr(bias), None, 1.0, native.ptr(st), off, keep, None, None)
     _run_plan(plan)
     return out
 
@@ -95,7 +95,7 @@ def linear_dx(dy: torch.Tensor, w: torch.Tensor, mask_act: Optional[torch.Tensor
     out = torch.empty(B, K, device=dy.device, dtype=torch.float32)
     plan = native.lib().ddl_tc_plan_act(1, native.ptr(dy), native.ptr(w), native.ptr(out), B, 1, 1, N, K, 1, ntile, 1,
                                         EPI_MASKPOS if mask_act is not None else 0, None, native.ptr(mask_act),
-                                        mask_scale, None, 0, 1.0, native.ptr(colsum))
+                                        mask_scale, None, 0, 1.0, native.ptr(colsum), None)
     _run_plan(plan)
     return out
 

@@ -55,7 +55,8 @@ class AsyncArgs(C.Structure):
 class EngineCfg(C.Structure):
     _fields_ = [("kind", C.c_int), ("width_mult", C.c_int), ("batch", C.c_int), ("max_eval_batch", C.c_int),
                 ("keep_prob", C.c_float), ("params", C.c_void_p), ("grads", C.c_void_p),
-                ("arena_elems", C.c_int64), ("var_offset", C.c_int64 * 16), ("st", C.c_void_p)]
+                ("arena_elems", C.c_int64), ("var_offset", C.c_int64 * 16), ("st", C.c_void_p),
+                ("fc_w_src", C.c_void_p * 2)]
 
 
 _LIB: Optional[C.CDLL] = None
@@ -101,7 +102,7 @@ def lib() -> C.CDLL:
         "ddl_fc3_bwd": ([vp, vp, vp, vp, vp, vp, i32, i32, i32, u32, u32, f32, vp], i32),
         "ddl_fc3_bwd_st": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, u32, f32, vp], i32),
         "ddl_accuracy": ([vp, vp, vp, i32, i32, vp], i32),
-        "ddl_tc_plan_act": ([i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, f32, vp, u32, f32, vp], vp),
+        "ddl_tc_plan_act": ([i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, f32, vp, u32, f32, vp, vp], vp),
         "ddl_tc_plan_wgrad": ([vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_tc_plan_run": ([vp, vp], i32),
         "ddl_tc_plan_destroy": ([vp], None),

@@ -117,7 +117,8 @@ class SPMDTrainer:
         if cfg.resume:
             self._load_opt_state(cfg.resume)
         self.model = Model(self.spec, self.params, self.grads, cfg, step_state=getattr(self.transport, "st", None),
-                           worker=lay.my_worker or 0, num_workers=lay.num_workers) if lay.is_worker else None
+                           worker=lay.my_worker or 0, num_workers=lay.num_workers,
+                           fc_w_src=getattr(self.transport, "k4_src", None)) if lay.is_worker else None
         self.transport.initial_sync()
         if lay.is_worker:
             self.x_test = self.data.x_test.to(self.device)
@@ -205,6 +206,8 @@ class SPMDTrainer:
         return self.transport.loss(cfg.batch_size) if lay.is_worker else None
 
     def evaluate(self) -> float:
+        if hasattr(self.transport, "ensure_local"):
+            self.transport.ensure_local()
         return self.model.accuracy(self.x_test, self.y_test)
 
     def run(self) -> Dict[str, object]:
@@ -251,6 +254,8 @@ class SPMDTrainer:
         return stats
 
     def save(self, path: str) -> None:
+        if hasattr(self.transport, "ensure_local"):
+            self.transport.ensure_local()
         st = self.transport.opt_state()
         if self.layout.rank == 0:
             save_checkpoint(path, self.params, st.get("m"), st.get("v"), int(st.get("t", 0)),

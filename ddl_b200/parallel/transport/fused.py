@@ -167,6 +167,25 @@ class FusedTransport(SpmdTransport):
             for k in range(native.MAX_SKIP):
                 a.skip_begin[k] = a.skip_end[k] = -1
             self.sync_args.append(a)
+        # ---- K4: variables whose pull is fused into their first consumer GEMM (fc1 / fc2 weights: each weight
+        # byte is read exactly once per step by the [B<=128 x K] x [K x N] matmul, so fetching the tiles
+        # straight from the owner over NVLink costs the same bytes as an all-gather and removes it).
+        # Their owners do not broadcast those ranges; the consumer writes them through to its local arena.
+        self.k4_src: Dict[int, Optional[int]] = {}
+        spec = params.spec
+        if (cfg.fused_pull_gemm and cfg.mode == "sync" and lay.world > 1 and self.plan.policy != "flat"
+                and spec.kind == "cnn"):
+            k = 0
+            for v in (8, 10):
+                owner_rank = lay.owner_rank(self.plan.owner[v])
+                b = self.plan.var_offset[v]
+                e = b + spec.vars[v].numel
+                self.k4_src[v] = None if owner_rank == lay.rank else mem["params"].ptrs[owner_rank] + 4 * b
+                if owner_rank == lay.rank:
+                    for a in self.sync_args:
+                        if a.begin <= b and e <= a.end:
+                            a.skip_begin[k], a.skip_end[k] = b, e
+                k += 1
         self.async_args = native.AsyncArgs()
         aa = self.async_args
         aa.num_shards = lay.num_ps
@@ -195,6 +214,12 @@ class FusedTransport(SpmdTransport):
         native.check(self.L.ddl_pull_allgather(C.byref(self.comm), C.byref(self.async_args), self._s()),
                      "ddl_pull_allgather")
         native.count()
+
+    def ensure_local(self) -> None:
+        """Make this rank's parameter arena complete and current (evaluation, checkpoints, inspection):
+        with K4 the fc1 / fc2 weights are only refreshed by the next training forward."""
+        if self.k4_src and self.layout.world > 1:
+            self.pull_all()
 
     def initial_sync(self) -> None:
         """Initial pull (Q5): every rank copies each owner's range; owners are the source of truth."""

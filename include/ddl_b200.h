@@ -84,12 +84,17 @@ int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int 
  *   wgrad plan:        out[tap][b][a] += sum_pix g[pix,a] * x[pix+off(tap), b]
  * flags: 1 bias, 2 relu, 4 dropout (seed/stream from st), 8 multiply by (mask_act > 0) * mask_scale.
  * ksplit > 1 accumulates raw sums with red.add into a pre-zeroed out (no bias/relu/dropout).
- * colsum (may be NULL): += per-column sums of the final output values (a bias gradient). */
+ * colsum (may be NULL): += per-column sums of the final output values (a bias gradient).
+ * w_store_dst (may be NULL; fprop only) - K4, the pull fused into the consumer GEMM: `w` may then point
+ * into ANOTHER rank's parameter arena (a peer-mapped pointer): the weight tiles are TMA-loaded over
+ * NVLink straight into the MMA's shared-memory stage and written through to w_store_dst (this rank's
+ * copy, same layout) by a TMA store, so no separate all-gather of that variable is needed
+ * (SS/ps.py:126 + SS/worker.py:94,97 + model.py:70,79 in one kernel). */
 typedef struct DdlTcPlan DdlTcPlan;
 DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
                            int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
                            const float* mask_act, float mask_scale, const DdlStepState* st,
-                           uint32_t drop_stream_off, float keep_prob, float* colsum);
+                           uint32_t drop_stream_off, float keep_prob, float* colsum, float* w_store_dst);
 DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,
                              int ksize, int ntile, int psplit);
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);
@@ -181,6 +186,8 @@ typedef struct DdlEngineCfg {
   int64_t arena_elems;
   int64_t var_offset[16];   /* element offset of v0..v13 in both arenas          */
   DdlStepState* st;
+  const float* fc_w_src[2]; /* K4: where the training forward fetches the fc1 / fc2 weight matrices from -
+                               the OWNER's arena (peer pointer); NULL = this rank's own copy            */
 } DdlEngineCfg;
 typedef struct DdlEngine DdlEngine;
 DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg);

@@ -37,6 +37,7 @@ def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd"):
     nb = 5
     for i in range(nb):
         tr.train_step(i)
+        tr.transport.ensure_local()             # K4: fc1/fc2 weights are otherwise refreshed by the next forward
         torch.cuda.synchronize()
         allp = gather_flat(tr.params.flat.clone())
         wr = tr.layout.worker_ranks
@@ -47,6 +48,11 @@ def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd"):
             assert torch.equal(allp[tr.layout.owner_rank(sh)][b:e], allp[wr[0]][b:e]), "owner range mismatch"
     st = tr.transport.stats()
     assert st["optimizer_steps"] == nb, st
+    if shard != "flat" and world > 1:
+        # K4 is live: the fc1 / fc2 forward GEMMs of non-owner workers read the owner's arena (peer pointer)
+        assert len(tr.transport.k4_src) == 2
+        if tr.layout.is_worker and layout_kind == "dedicated":
+            assert all(p is not None for p in tr.transport.k4_src.values())
     if graphs and tr.layout.is_worker:
         assert tr._graph is not None, "CUDA graph path was not taken"
     tr.transport.close()
@@ -75,6 +81,9 @@ def case_sync_vs_nccl(rank, world, layout_kind, shard, opt):
             tr.transport.step()
             torch.cuda.synchronize()
             dist.barrier()
+        if hasattr(tr.transport, "ensure_local"):
+            tr.transport.ensure_local()         # K4 ranges are refreshed by a training forward, which this test skips
+            torch.cuda.synchronize()
         results[transport] = tr.params.flat.clone()
         tr.transport.close()
     if rank in tr.layout.worker_ranks:

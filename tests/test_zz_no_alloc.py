@@ -36,7 +36,7 @@ def _reference(L, native, x, w, b):
     raw = torch.empty(N, H, W, cout, device=x.device)
     nt = 128 if cout % 128 == 0 else 64 if cout % 64 == 0 else 32
     plan = L.ddl_tc_plan_act(0, x.data_ptr(), w.data_ptr(), raw.data_ptr(), N, H, W, cin, cout, 5, nt, 1, 0,
-                             None, None, 1.0, None, 0, 1.0, None)
+                             None, None, 1.0, None, 0, 1.0, None, None)
     assert plan, native.last_error()
     s = torch.cuda.current_stream().cuda_stream
     assert L.ddl_tc_plan_run(plan, s) == 0, native.last_error()

@@ -27,7 +27,7 @@ def act(dgrad, N, H, cred, nout, ks, ntile, ksplit=1):
     w = torch.randn(ks * ks * cred * nout, device=dev) * 0.05
     out = torch.zeros(N, H, H, nout, device=dev)
     plan = L.ddl_tc_plan_act(dgrad, x.data_ptr(), w.data_ptr(), out.data_ptr(), N, H, H, cred, nout, ks, ntile, ksplit, 0,
-                             None, None, 1.0, None, 0, 1.0, None)
+                             None, None, 1.0, None, 0, 1.0, None, None)
     assert plan, native.last_error()
     import ctypes as C
     info = (C.c_int * 8)(); L.ddl_tc_plan_info(plan, info)

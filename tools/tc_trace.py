@@ -8,7 +8,7 @@ L.ddl_tc_plan_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 dev = torch.device("cuda")
 N, cred, nout = 128, 2048, 32
 x = torch.randn(N, cred, device=dev); w = torch.randn(cred * nout, device=dev); out = torch.zeros(N, nout, device=dev)
-plan = L.ddl_tc_plan_act(0, x.data_ptr(), w.data_ptr(), out.data_ptr(), N, 1, 1, cred, nout, 1, 32, 1, 0, None, None, 1.0, None, 0, 1.0, None)
+plan = L.ddl_tc_plan_act(0, x.data_ptr(), w.data_ptr(), out.data_ptr(), N, 1, 1, cred, nout, 1, 32, 1, 0, None, None, 1.0, None, 0, 1.0, None, None)
 for _ in range(3):
     L.ddl_tc_plan_run(plan, native.stream_ptr())
 torch.cuda.synchronize()
