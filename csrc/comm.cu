@@ -129,14 +129,19 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
       }
     }
   }
-  // ---- barrier B: last block to finish publishes "my range is delivered" and waits for the others
-  __threadfence_system();
+  // ---- barrier B: last block to finish publishes "my range is delivered" and waits for the others.
+  // One fence per block, not per thread: bar.sync makes the block's stores observed by thread 0, whose
+  // (cumulative) fence then orders them before the counter bump - the cooperative-groups grid-sync idiom.
+  // A system-scope fence is only needed when stores went to peers.
   __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  if (threadIdx.x == 0) {
+    if (c.world > 1) __threadfence_system(); else __threadfence();
+    s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
   __syncthreads();
   if (s_last) {
-    if (threadIdx.x == 0) *a.done_counter = 0;
-    __threadfence_system();
+    if (threadIdx.x == 0) { *a.done_counter = 0; __threadfence_system(); }
+    __syncthreads();
     pad_signal(c, 0, epochB);
     pad_wait(c, 0, epochB);
   }
@@ -164,13 +169,15 @@ async_push_kernel(const DdlComm c, const DdlAsyncArgs a) {
       red_add_v4_f32(dst + i, x);
     }
   }
-  __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  if (threadIdx.x == 0) {
+    __threadfence_system();                      // this block's remote reds are performed (cumulative after bar.sync)
+    s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
   __syncthreads();
   if (s_last) {
-    if (threadIdx.x == 0) *a.done_counter = 0;
-    __threadfence_system();
+    if (threadIdx.x == 0) { *a.done_counter = 0; __threadfence_system(); }
+    __syncthreads();
     // one release-ordered counter bump per owner: "a complete push has landed"
     if ((int)threadIdx.x < a.num_shards) {
       const int owner = a.owner_rank[threadIdx.x];
@@ -217,9 +224,11 @@ async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const uint32_t* pending
     const float4 pn = opt_apply<KIND>(*reinterpret_cast<float4*>(myp + i), g, a.m, a.v, i, step, a.a, a.b, a.eps);
     *reinterpret_cast<float4*>(myp + i) = pn;
   }
-  __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+  }
   __syncthreads();
   if (s_last && threadIdx.x == 0) {
     *a.done_counter = 0;

@@ -147,41 +147,46 @@ __global__ void conv1_relu_pool_kernel(const float* __restrict__ x, const float*
 }
 
 // conv1 weight / bias gradient.  dY is the full-resolution gradient [B,S,S,C] (after pool-bwd).
-// One block = half an image (S/2 rows) x 32 channels: the dY tile and the zero-padded x halo are staged
-// in shared memory once, then warp t accumulates tap t (t = 25: the bias) with lane = channel, so the
-// inner loop is two LDS + one FMA per pixel.  grid = (2*B, C/32); block = 26 warps.
-__global__ void __launch_bounds__(832) conv1_wgrad_kernel(const float* __restrict__ x,
+// A thread owns one channel and one filter ROW (kh): it walks its strip of pixels left to right keeping
+// the five x values under the filter row in a register window, so each pixel costs one dY load, one x
+// load and five FMAs for five taps.  Block = 32 channels x 5 filter rows (+ warp 5: the bias);
+// grid = (B * strips, C/32) with strips of S/4 image rows.
+__global__ void __launch_bounds__(192) conv1_wgrad_kernel(const float* __restrict__ x,
                                                           const float* __restrict__ dy,
                                                           float* __restrict__ dw, float* __restrict__ db,
-                                                          int B, int S, int C) {
-  extern __shared__ float sm[];
-  const int rows = S / 2, XP = S + 4;
-  float* sdy = sm;                               // [rows*S][32]
-  float* sx = sm + rows * S * 32;                // [(rows+4)][S+4], zero padded
-  const int n = blockIdx.x >> 1, half = blockIdx.x & 1;
-  const int h0 = half * rows, cg = blockIdx.y * 32;
-  const int lane = threadIdx.x & 31, tap = threadIdx.x >> 5;
-  const float* dyi = dy + ((int64_t)n * S * S + (int64_t)h0 * S) * C + cg;
-  for (int i = threadIdx.x; i < rows * S * 32; i += blockDim.x)
-    sdy[i] = dyi[(int64_t)(i >> 5) * C + (i & 31)];
-  for (int i = threadIdx.x; i < (rows + 4) * XP; i += blockDim.x) {
+                                                          int B, int S, int C, int strip) {
+  extern __shared__ float sx[];                  // [(strip+4)][S+4] zero-padded x rows of this strip
+  const int XP = S + 4;
+  const int strips = S / strip;
+  const int n = blockIdx.x / strips, h0 = (blockIdx.x % strips) * strip;
+  const int cg = blockIdx.y * 32;
+  const int lane = threadIdx.x & 31, kh = threadIdx.x >> 5;      // kh = 5: bias warp
+  for (int i = threadIdx.x; i < (strip + 4) * XP; i += blockDim.x) {
     const int r = i / XP + h0 - 2, cc = i % XP - 2;
     sx[i] = (r >= 0 && r < S && cc >= 0 && cc < S) ? x[(int64_t)n * S * S + r * S + cc] : 0.f;
   }
   __syncthreads();
-  float acc = 0.f;
-  if (tap < 25) {
-    const int kh = tap / 5, kw = tap % 5;
-    for (int py = 0; py < rows; ++py) {
-      const float* xr = sx + (py + kh) * XP + kw;
-      const float* gr = sdy + py * S * 32 + lane;
+  const float* dyi = dy + ((int64_t)n * S * S + (int64_t)h0 * S) * C + cg + lane;
+  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  if (kh < 5) {
+    for (int py = 0; py < strip; ++py) {
+      const float* xr = sx + (py + kh) * XP;     // x row under filter row kh for output row py
+      float w0 = xr[0], w1 = xr[1], w2 = xr[2], w3 = xr[3];
+      const float* gr = dyi + (int64_t)py * S * C;
 #pragma unroll 4
-      for (int px = 0; px < S; ++px) acc += xr[px] * gr[px * 32];
+      for (int px = 0; px < S; ++px) {
+        const float w4 = xr[px + 4];
+        const float g = gr[(int64_t)px * C];
+        acc[0] += w0 * g; acc[1] += w1 * g; acc[2] += w2 * g; acc[3] += w3 * g; acc[4] += w4 * g;
+        w0 = w1; w1 = w2; w2 = w3; w3 = w4;
+      }
     }
-    atomicAdd(dw + tap * C + cg + lane, acc);
+#pragma unroll
+    for (int kw = 0; kw < 5; ++kw) atomicAdd(dw + (kh * 5 + kw) * C + cg + lane, acc[kw]);
   } else {
-    for (int i = 0; i < rows * S; ++i) acc += sdy[i * 32 + lane];
-    atomicAdd(db + cg + lane, acc);
+    float s2 = 0.f;
+    for (int i = 0; i < strip * S; ++i) s2 += dyi[(int64_t)i * C];
+    atomicAdd(db + cg + lane, s2);
   }
 }
 
@@ -456,16 +461,10 @@ int ddl_conv1_relu_pool(const float* x, const float* w, const float* bias, float
 
 int ddl_conv1_wgrad(const float* x, const float* dy, float* dw, float* db, int B, int S, int C, cudaStream_t s) {
   DDL_REQUIRE(C % 32 == 0, "ddl_conv1_wgrad: C %% 32 == 0");
-  DDL_REQUIRE(S % 2 == 0, "ddl_conv1_wgrad: S must be even");
-  dim3 grid(2 * B, C / 32);
-  const size_t smem = ((size_t)(S / 2) * S * 32 + (size_t)(S / 2 + 4) * (S + 4)) * sizeof(float);
-  static bool attr_done = false;
-  if (!attr_done) {
-    DDL_CHECK_CUDA(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr_done = true;
-  }
-  DDL_REQUIRE(smem <= 100 * 1024, "ddl_conv1_wgrad: tile does not fit shared memory");
-  conv1_wgrad_kernel<<<grid, 832, smem, s>>>(x, dy, dw, db, B, S, C);
+  const int strip = (S % 4 == 0) ? S / 4 : (S % 2 == 0 ? S / 2 : S);
+  dim3 grid(B * (S / strip), C / 32);
+  const size_t smem = (size_t)(strip + 4) * (S + 4) * sizeof(float);
+  conv1_wgrad_kernel<<<grid, 192, smem, s>>>(x, dy, dw, db, B, S, C, strip);
   DDL_LAUNCH_CHECK();
   return 0;
 }
