@@ -92,6 +92,7 @@ DDL_DEVICE float4 opt_apply(float4 pv, float4 gv, float* m, float* v, int64_t i,
 template <int KIND>
 __global__ void __launch_bounds__(kCommThreads)
 sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
+  pdl_enter();
   __shared__ uint32_t s_last;
   const uint32_t t = a.st->t;                       // same on every rank: all ranks advance together
   const uint32_t epochA = 2u * t + 1u, epochB = 2u * t + 2u;
@@ -154,6 +155,7 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kCommThreads)
 async_push_kernel(const DdlComm c, const DdlAsyncArgs a) {
+  pdl_enter();
   __shared__ uint32_t s_last;
   const float* g = c.grads[c.rank];
   for (int o = 0; o < a.num_shards; ++o) {
@@ -193,6 +195,7 @@ async_push_kernel(const DdlComm c, const DdlAsyncArgs a) {
 // owner: 1 thread decides whether pushes are pending and advances the shard's step state
 __global__ void async_snapshot_kernel(const DdlComm c, DdlStepState* st, uint32_t* applied, uint32_t* pending,
                                       float lr, float b1, float b2) {
+  pdl_enter();
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     const uint32_t pushes = ld_acquire_sys(c.pads[c.rank] + DDL_PAD_PUSHES);
     const uint32_t n = pushes - *applied;
@@ -209,6 +212,7 @@ __global__ void async_snapshot_kernel(const DdlComm c, DdlStepState* st, uint32_
 template <int KIND>
 __global__ void __launch_bounds__(kCommThreads)
 async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const uint32_t* pending) {
+  pdl_enter();
   __shared__ uint32_t s_last;
   if (*pending == 0) return;
   const float step = (KIND == 2) ? a.st->lr_t : a.lr;
@@ -240,6 +244,7 @@ async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const uint32_t* pending
 // K3: worker copies every owner's range into its own parameter arena (peer loads, no barrier).
 __global__ void __launch_bounds__(kCommThreads)
 pull_allgather_kernel(const DdlComm c, const DdlAsyncArgs a) {
+  pdl_enter();
   float* myp = c.params[c.rank];
   for (int o = 0; o < a.num_shards; ++o) {
     const int owner = a.owner_rank[o];
@@ -256,6 +261,7 @@ pull_allgather_kernel(const DdlComm c, const DdlAsyncArgs a) {
 }
 
 __global__ void device_barrier_kernel(const DdlComm c, uint32_t* epoch_counter) {
+  pdl_enter();
   __shared__ uint32_t e;
   if (threadIdx.x == 0) e = ++(*epoch_counter);
   __syncthreads();
@@ -306,9 +312,9 @@ int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, 
   DDL_REQUIRE(c->world >= 1 && c->world <= DDL_MAX_PEERS, "world %d out of range", c->world);
   DDL_REQUIRE(a->begin % 4 == 0 && a->end % 4 == 0, "shard range must be float4 aligned");
   const int grid = comm_grid(a->end - a->begin);
-  if (kind == 0) sync_push_update_pull_kernel<0><<<grid, kCommThreads, 0, s>>>(*c, *a);
-  else if (kind == 1) sync_push_update_pull_kernel<1><<<grid, kCommThreads, 0, s>>>(*c, *a);
-  else sync_push_update_pull_kernel<2><<<grid, kCommThreads, 0, s>>>(*c, *a);
+  if (kind == 0) DDL_LAUNCH(sync_push_update_pull_kernel<0>, grid, kCommThreads, 0, s, *c, *a);
+  else if (kind == 1) DDL_LAUNCH(sync_push_update_pull_kernel<1>, grid, kCommThreads, 0, s, *c, *a);
+  else DDL_LAUNCH(sync_push_update_pull_kernel<2>, grid, kCommThreads, 0, s, *c, *a);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -316,18 +322,18 @@ int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, 
 int ddl_async_push(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s) {
   int64_t total = 0;
   for (int o = 0; o < a->num_shards; ++o) total += a->shard_end[o] - a->shard_begin[o];
-  async_push_kernel<<<comm_grid(total), kCommThreads, 0, s>>>(*c, *a);
+  DDL_LAUNCH(async_push_kernel, comm_grid(total), kCommThreads, 0, s, *c, *a);
   DDL_LAUNCH_CHECK();
   return 0;
 }
 
 int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, uint32_t* applied, uint32_t* pending,
                     float b1, float b2, cudaStream_t s) {
-  async_snapshot_kernel<<<1, 32, 0, s>>>(*c, a->st, applied, pending, a->lr, b1, b2);
+  DDL_LAUNCH(async_snapshot_kernel, 1, 32, 0, s, *c, a->st, applied, pending, a->lr, b1, b2);
   const int grid = comm_grid(a->end - a->begin);
-  if (kind == 0) async_apply_kernel<0><<<grid, kCommThreads, 0, s>>>(*c, *a, pending);
-  else if (kind == 1) async_apply_kernel<1><<<grid, kCommThreads, 0, s>>>(*c, *a, pending);
-  else async_apply_kernel<2><<<grid, kCommThreads, 0, s>>>(*c, *a, pending);
+  if (kind == 0) DDL_LAUNCH(async_apply_kernel<0>, grid, kCommThreads, 0, s, *c, *a, pending);
+  else if (kind == 1) DDL_LAUNCH(async_apply_kernel<1>, grid, kCommThreads, 0, s, *c, *a, pending);
+  else DDL_LAUNCH(async_apply_kernel<2>, grid, kCommThreads, 0, s, *c, *a, pending);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -335,13 +341,13 @@ int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, uint32_t* 
 int ddl_pull_allgather(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s) {
   int64_t total = 0;
   for (int o = 0; o < a->num_shards; ++o) total += a->shard_end[o] - a->shard_begin[o];
-  pull_allgather_kernel<<<comm_grid(total), kCommThreads, 0, s>>>(*c, *a);
+  DDL_LAUNCH(pull_allgather_kernel, comm_grid(total), kCommThreads, 0, s, *c, *a);
   DDL_LAUNCH_CHECK();
   return 0;
 }
 
 int ddl_device_barrier(const DdlComm* c, uint32_t* epoch_counter, cudaStream_t s) {
-  device_barrier_kernel<<<1, 32, 0, s>>>(*c, epoch_counter);
+  DDL_LAUNCH(device_barrier_kernel, 1, 32, 0, s, *c, epoch_counter);
   DDL_LAUNCH_CHECK();
   return 0;
 }

@@ -35,6 +35,33 @@ const char* get_error();
 
 #define DDL_LAUNCH_CHECK() DDL_CHECK_CUDA(cudaGetLastError())
 
+namespace ddl {
+bool pdl_enabled();        // DDL_PDL=0 disables programmatic dependent launch
+// one launch path for every kernel: PDL attribute (+ optional cluster along z)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                          unsigned cluster_z, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster_z > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = 1; attr[n].val.clusterDim.y = 1; attr[n].val.clusterDim.z = cluster_z;
+    ++n;
+  }
+  cfg.attrs = attr; cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+}  // namespace ddl
+#define DDL_LAUNCH(kernel, grid, block, smem, stream, ...) \
+  DDL_CHECK_CUDA(ddl::launch(kernel, dim3(grid), dim3(block), smem, stream, 1u, __VA_ARGS__))
+
 // ------------------------------------------------------------------------------------ misc device
 #define DDL_DEVICE __device__ __forceinline__
 
@@ -242,6 +269,23 @@ __host__ __device__ inline uint32_t umma_idesc_tf32(int M, int N, int a_mn_major
   d |= (uint32_t)(M >> 4) << 24;
   return d;
 }
+
+// ------------------------------------------------------------------------------------ programmatic dependent launch
+// Every kernel of this library is launched with programmatic stream serialization (PDL): it may begin
+// while its predecessor in the stream is still running, so launch latency, block scheduling and the
+// smem / mbarrier / TMEM prologue overlap the predecessor's tail.  Contract for every kernel:
+//   pdl_launch_dependents() first (lets the successor start early), then pdl_wait() before the first
+//   access to global memory - it returns once the predecessor grid has completed and flushed.
+// EVERY thread of EVERY kernel executes pdl_wait(), also on early-exit paths: a grid that finishes
+// without waiting would let its own successor overtake the grid it skipped.
+DDL_DEVICE void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+DDL_DEVICE void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+DDL_DEVICE void pdl_enter() { pdl_launch_dependents(); pdl_wait(); }
+
+// ------------------------------------------------------------------------------------ thread-block clusters
+DDL_DEVICE uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+DDL_DEVICE void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+DDL_DEVICE void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------------------------ system-scope sync
 DDL_DEVICE void st_release_sys(uint32_t* p, uint32_t v) {

@@ -22,6 +22,7 @@ inline int grid_for(int64_t n, int per_block, int cap = 148 * 8) {
 
 // ------------------------------------------------------------------------------------ step state
 __global__ void step_advance_kernel(DdlStepState* st, float lr, float b1, float b2, int advance_opt) {
+  pdl_enter();
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     const uint32_t ws = st->wstep + 1;
     st->wstep = ws;
@@ -44,6 +45,7 @@ template <int KIND>
 __global__ void optimizer_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
                                  const float* __restrict__ g, int64_t n4, int64_t n, float step_size,
                                  float a, float b, float eps, float gscale, const DdlStepState* st) {
+  pdl_enter();
   if (st != nullptr && KIND == 2) step_size = st->lr_t;
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -94,55 +96,70 @@ __global__ void optimizer_kernel(float* __restrict__ p, float* __restrict__ m, f
 }
 
 // ------------------------------------------------------------------------------------ conv1 (Cin = 1)
-// One thread = one pooled output pixel x one channel: computes the 2x2 block of 5x5 SAME conv
-// outputs, bias, ReLU, max -> pooled value + 2-bit argmax (4 = "max is 0, no gradient").
-// x [B,S,S] (Cin = 1), w [25][C], y [B,S/2,S/2,C].  S even.
-__global__ void conv1_relu_pool_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                       const float* __restrict__ bias, float* __restrict__ y,
-                                       uint8_t* __restrict__ idx, int B, int S, int C) {
-  extern __shared__ float sw[];          // [25][C] weights + [C] bias
+// One block = one image: the zero-padded image ((S+4)^2 floats) and the filter bank live in shared
+// memory, so the inner loop has no bounds checks.  A work item = one pooled pixel x 4 channels: the 6x6
+// input patch is read once (broadcast LDS) and reused for 4 channels x 4 conv outputs (2x2 pool window);
+// weights come as float4.  Output: bias + ReLU + 2x2 max-pool, 2-bit arg-max (4 = "max is 0").
+// x [B,S,S] (Cin = 1), w [25][C], y [B,S/2,S/2,C].  S even, C % 4 == 0.
+__global__ void __launch_bounds__(256) conv1_relu_pool_kernel(const float* __restrict__ x,
+                                                              const float* __restrict__ w,
+                                                              const float* __restrict__ bias,
+                                                              float* __restrict__ y, uint8_t* __restrict__ idx,
+                                                              int B, int S, int C) {
+  pdl_enter();
+  extern __shared__ float sm1[];
+  const int XP = S + 4;
+  float* sw = sm1;                         // [25][C] + [C] bias
+  float* sx = sm1 + 26 * C;                // [(S+4)][(S+4)]
+  const int n = blockIdx.x;
   for (int i = threadIdx.x; i < 25 * C; i += blockDim.x) sw[i] = w[i];
   for (int i = threadIdx.x; i < C; i += blockDim.x) sw[25 * C + i] = bias[i];
+  for (int i = threadIdx.x; i < XP * XP; i += blockDim.x) {
+    const int r = i / XP - 2, cc = i % XP - 2;
+    sx[i] = (r >= 0 && r < S && cc >= 0 && cc < S) ? x[(int64_t)n * S * S + r * S + cc] : 0.f;
+  }
   __syncthreads();
-  const int P = S / 2;
-  int64_t total = (int64_t)B * P * P * C;
-  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < total;
-       t += (int64_t)gridDim.x * blockDim.x) {
-    int c = (int)(t % C);
-    int64_t pix = t / C;
-    int pw = (int)(pix % P), ph = (int)((pix / P) % P), n = (int)(pix / ((int64_t)P * P));
-    const float* xi = x + (int64_t)n * S * S;
+  const int P = S / 2, C4 = C / 4;
+  const int items = P * P * C4;
+  for (int t = threadIdx.x; t < items; t += blockDim.x) {
+    const int c4 = t % C4, pix = t / C4;
+    const int pw = pix % P, ph = pix / P;
     float patch[6][6];
 #pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      int h = 2 * ph - 2 + i;
+    for (int i = 0; i < 6; ++i)
 #pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        int ww = 2 * pw - 2 + j;
-        patch[i][j] = (h >= 0 && h < S && ww >= 0 && ww < S) ? __ldg(xi + h * S + ww) : 0.f;
-      }
-    }
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int j = 0; j < 6; ++j) patch[i][j] = sx[(2 * ph + i) * XP + 2 * pw + j];
+    float acc[4][4];                       // [window position][channel]
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[k][q] = 0.f;
 #pragma unroll
     for (int kh = 0; kh < 5; ++kh)
 #pragma unroll
       for (int kw = 0; kw < 5; ++kw) {
-        float wv = sw[(kh * 5 + kw) * C + c];
-        acc[0] += patch[kh][kw] * wv;
-        acc[1] += patch[kh][kw + 1] * wv;
-        acc[2] += patch[kh + 1][kw] * wv;
-        acc[3] += patch[kh + 1][kw + 1] * wv;
-      }
-    float bv = sw[25 * C + c];
-    float best = 0.f;
-    int bi = 4;
+        const float4 wv = *reinterpret_cast<const float4*>(sw + (kh * 5 + kw) * C + c4 * 4);
+        const float ww[4] = {wv.x, wv.y, wv.z, wv.w};
+        const float p0 = patch[kh][kw], p1 = patch[kh][kw + 1], p2 = patch[kh + 1][kw], p3 = patch[kh + 1][kw + 1];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      float a = acc[k] + bv;
-      if (a > best) { best = a; bi = k; }
-    }
-    y[t] = best;
-    if (idx) idx[t] = (uint8_t)bi;
+        for (int q = 0; q < 4; ++q) {
+          acc[0][q] += p0 * ww[q]; acc[1][q] += p1 * ww[q]; acc[2][q] += p2 * ww[q]; acc[3][q] += p3 * ww[q];
+        }
+      }
+    const float4 bv4 = *reinterpret_cast<const float4*>(sw + 25 * C + c4 * 4);
+    const float bb[4] = {bv4.x, bv4.y, bv4.z, bv4.w};
+    float best[4] = {0.f, 0.f, 0.f, 0.f};
+    int bi[4] = {4, 4, 4, 4};
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float a = acc[k][q] + bb[q];
+        if (a > best[q]) { best[q] = a; bi[q] = k; }
+      }
+    const int64_t o = ((int64_t)n * P * P + pix) * C + c4 * 4;
+    *reinterpret_cast<float4*>(y + o) = make_float4(best[0], best[1], best[2], best[3]);
+    if (idx) *reinterpret_cast<uchar4*>(idx + o) = make_uchar4(bi[0], bi[1], bi[2], bi[3]);
   }
 }
 
@@ -151,10 +168,12 @@ __global__ void conv1_relu_pool_kernel(const float* __restrict__ x, const float*
 // the five x values under the filter row in a register window, so each pixel costs one dY load, one x
 // load and five FMAs for five taps.  Block = 32 channels x 5 filter rows (+ warp 5: the bias);
 // grid = (B * strips, C/32) with strips of S/4 image rows.
+template <int S>
 __global__ void __launch_bounds__(192) conv1_wgrad_kernel(const float* __restrict__ x,
                                                           const float* __restrict__ dy,
                                                           float* __restrict__ dw, float* __restrict__ db,
-                                                          int B, int S, int C, int strip) {
+                                                          int B, int C, int strip) {
+  pdl_enter();
   extern __shared__ float sx[];                  // [(strip+4)][S+4] zero-padded x rows of this strip
   const int XP = S + 4;
   const int strips = S / strip;
@@ -173,10 +192,10 @@ __global__ void __launch_bounds__(192) conv1_wgrad_kernel(const float* __restric
       const float* xr = sx + (py + kh) * XP;     // x row under filter row kh for output row py
       float w0 = xr[0], w1 = xr[1], w2 = xr[2], w3 = xr[3];
       const float* gr = dyi + (int64_t)py * S * C;
-#pragma unroll 4
-      for (int px = 0; px < S; ++px) {
+#pragma unroll
+      for (int px = 0; px < S; ++px) {       // fully unrolled: the register window rotates for free
         const float w4 = xr[px + 4];
-        const float g = gr[(int64_t)px * C];
+        const float g = gr[px * C];
         acc[0] += w0 * g; acc[1] += w1 * g; acc[2] += w2 * g; acc[3] += w3 * g; acc[4] += w4 * g;
         w0 = w1; w1 = w2; w2 = w3; w3 = w4;
       }
@@ -197,6 +216,7 @@ __global__ void __launch_bounds__(192) conv1_wgrad_kernel(const float* __restric
 __global__ void maxpool_fwd_kernel(const float* __restrict__ a, const float* __restrict__ bias,
                                    float* __restrict__ y, uint8_t* __restrict__ idx,
                                    int B, int H, int W, int C) {
+  pdl_enter();
   const int PH = (H + 1) / 2, PW = (W + 1) / 2;
   const int C4 = C / 4;
   int64_t total = (int64_t)B * PH * PW * C4;
@@ -234,6 +254,7 @@ __global__ void maxpool_fwd_kernel(const float* __restrict__ a, const float* __r
 __global__ void maxpool_bwd_kernel(const float* __restrict__ dp, const uint8_t* __restrict__ idx,
                                    float* __restrict__ dy, float* __restrict__ db,
                                    int B, int H, int W, int C) {
+  pdl_enter();
   extern __shared__ float sb[];           // [C] bias-gradient partials
   const int PH = (H + 1) / 2, PW = (W + 1) / 2;
   const int C4 = C / 4;
@@ -275,6 +296,7 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dp, const uint8_t* 
 // ------------------------------------------------------------------------------------ column sums
 // out[c] += sum_r x[r, c]   (bias gradients of the FC layers)
 __global__ void colsum_kernel(const float* __restrict__ x, float* __restrict__ out, int R, int C) {
+  pdl_enter();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float s = 0.f;
@@ -289,6 +311,7 @@ __global__ void fc3_xent_fwd_kernel(const float* __restrict__ h, const float* __
                                     const float* __restrict__ bias, const int* __restrict__ labels,
                                     float* __restrict__ logits, float* __restrict__ dlogits,
                                     DdlStepState* st, int B, int K, int NC, float scale, int use_smem) {
+  pdl_enter();
   extern __shared__ float sw3[];            // [K][NC] when use_smem
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -354,6 +377,7 @@ __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restr
                                float* __restrict__ dh, float* __restrict__ dbh, int B, int K, int NC,
                                uint32_t seed, uint32_t stream, uint32_t thresh24, float inv_keep,
                                const DdlStepState* st) {
+  pdl_enter();
   extern __shared__ float sm[];
   __shared__ float colred[8][32];
   if (st) { seed = st->seed; stream += st->stream; }
@@ -411,6 +435,7 @@ __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restr
 
 __global__ void accuracy_kernel(const float* __restrict__ logits, const int* __restrict__ labels,
                                 unsigned* __restrict__ correct, int B, int NC) {
+  pdl_enter();
   int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= B) return;
   float mx = logits[(int64_t)r * NC];
@@ -428,7 +453,7 @@ __global__ void accuracy_kernel(const float* __restrict__ logits, const int* __r
 extern "C" {
 
 int ddl_step_advance(DdlStepState* st, float lr, float b1, float b2, int advance_opt, cudaStream_t s) {
-  step_advance_kernel<<<1, 32, 0, s>>>(st, lr, b1, b2, advance_opt);
+  DDL_LAUNCH(step_advance_kernel, 1, 32, 0, s, st, lr, b1, b2, advance_opt);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -442,9 +467,9 @@ int ddl_optimizer_step(int kind, float* p, float* m, float* v, const float* g, i
   if (n <= 0) return 0;
   int64_t n4 = n / 4;
   int grid = grid_for(n4 > 0 ? n4 : 1, kThreads, 148 * 4);
-  if (kind == 0) optimizer_kernel<0><<<grid, kThreads, 0, s>>>(p, m, v, g, n4, n, step_size, a, b, eps, gscale, st);
-  else if (kind == 1) optimizer_kernel<1><<<grid, kThreads, 0, s>>>(p, m, v, g, n4, n, step_size, a, b, eps, gscale, st);
-  else optimizer_kernel<2><<<grid, kThreads, 0, s>>>(p, m, v, g, n4, n, step_size, a, b, eps, gscale, st);
+  if (kind == 0) DDL_LAUNCH(optimizer_kernel<0>, grid, kThreads, 0, s, p, m, v, g, n4, n, step_size, a, b, eps, gscale, st);
+  else if (kind == 1) DDL_LAUNCH(optimizer_kernel<1>, grid, kThreads, 0, s, p, m, v, g, n4, n, step_size, a, b, eps, gscale, st);
+  else DDL_LAUNCH(optimizer_kernel<2>, grid, kThreads, 0, s, p, m, v, g, n4, n, step_size, a, b, eps, gscale, st);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -452,9 +477,16 @@ int ddl_optimizer_step(int kind, float* p, float* m, float* v, const float* g, i
 int ddl_conv1_relu_pool(const float* x, const float* w, const float* bias, float* y, uint8_t* idx,
                         int B, int S, int C, cudaStream_t s) {
   DDL_REQUIRE(S % 2 == 0 && C % 32 == 0, "ddl_conv1_relu_pool: S even, C %% 32 == 0");
-  int64_t total = (int64_t)B * (S / 2) * (S / 2) * C;
-  size_t smem = (size_t)26 * C * sizeof(float);
-  conv1_relu_pool_kernel<<<grid_for(total, kThreads, 148 * 16), kThreads, smem, s>>>(x, w, bias, y, idx, B, S, C);
+  const size_t smem = ((size_t)26 * C + (size_t)(S + 4) * (S + 4)) * sizeof(float);
+  DDL_REQUIRE(smem <= 200 * 1024, "ddl_conv1_relu_pool: filter bank does not fit shared memory");
+  if (smem > 48 * 1024) {
+    static bool attr_done = false;
+    if (!attr_done) {
+      DDL_CHECK_CUDA(cudaFuncSetAttribute(conv1_relu_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_done = true;
+    }
+  }
+  DDL_LAUNCH(conv1_relu_pool_kernel, B, 256, smem, s, x, w, bias, y, idx, B, S, C);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -464,7 +496,9 @@ int ddl_conv1_wgrad(const float* x, const float* dy, float* dw, float* db, int B
   const int strip = (S % 4 == 0) ? S / 4 : (S % 2 == 0 ? S / 2 : S);
   dim3 grid(B * (S / strip), C / 32);
   const size_t smem = (size_t)(strip + 4) * (S + 4) * sizeof(float);
-  conv1_wgrad_kernel<<<grid, 192, smem, s>>>(x, dy, dw, db, B, S, C, strip);
+  if (S == 28) DDL_LAUNCH(conv1_wgrad_kernel<28>, grid, 192, smem, s, x, dy, dw, db, B, C, strip);
+  else if (S == 32) DDL_LAUNCH(conv1_wgrad_kernel<32>, grid, 192, smem, s, x, dy, dw, db, B, C, strip);
+  else DDL_REQUIRE(false, "ddl_conv1_wgrad: image size %d not instantiated (28, 32)", S);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -473,7 +507,7 @@ int ddl_maxpool_fwd(const float* a, const float* bias, float* y, uint8_t* idx, i
                     cudaStream_t s) {
   DDL_REQUIRE(C % 4 == 0, "ddl_maxpool_fwd: C %% 4 == 0");
   int64_t total = (int64_t)B * ((H + 1) / 2) * ((W + 1) / 2) * (C / 4);
-  maxpool_fwd_kernel<<<grid_for(total, kThreads, 148 * 16), kThreads, 0, s>>>(a, bias, y, idx, B, H, W, C);
+  DDL_LAUNCH(maxpool_fwd_kernel, grid_for(total, kThreads, 148 * 16), kThreads, 0, s, a, bias, y, idx, B, H, W, C);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -482,14 +516,14 @@ int ddl_maxpool_bwd(const float* dp, const uint8_t* idx, float* dy, float* db, i
                     cudaStream_t s) {
   DDL_REQUIRE(C % 4 == 0, "ddl_maxpool_bwd: C %% 4 == 0");
   int64_t total = (int64_t)B * ((H + 1) / 2) * ((W + 1) / 2) * (C / 4);
-  maxpool_bwd_kernel<<<grid_for(total, kThreads, 148 * 4), kThreads, C * sizeof(float), s>>>(dp, idx, dy, db, B, H, W, C);
+  DDL_LAUNCH(maxpool_bwd_kernel, grid_for(total, kThreads, 148 * 4), kThreads, C * sizeof(float), s, dp, idx, dy, db, B, H, W, C);
   DDL_LAUNCH_CHECK();
   return 0;
 }
 
 int ddl_colsum(const float* x, float* out, int R, int C, cudaStream_t s) {
   dim3 grid((C + 127) / 128, R >= 64 ? 8 : 1);
-  colsum_kernel<<<grid, 128, 0, s>>>(x, out, R, C);
+  DDL_LAUNCH(colsum_kernel, grid, 128, 0, s, x, out, R, C);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -499,8 +533,7 @@ int ddl_fc3_xent_fwd(const float* h, const float* w, const float* bias, const in
   DDL_REQUIRE(NC <= 16, "ddl_fc3_xent_fwd: at most 16 classes");
   const size_t wbytes = (size_t)K * NC * sizeof(float);
   const int use_smem = wbytes <= 48 * 1024 ? 1 : 0;
-  fc3_xent_fwd_kernel<<<(B + 7) / 8, 256, use_smem ? wbytes : 0, s>>>(h, w, bias, labels, logits, dlogits, st, B, K,
-                                                                       NC, scale, use_smem);
+  DDL_LAUNCH(fc3_xent_fwd_kernel, (B + 7) / 8, 256, use_smem ? wbytes : 0, s, h, w, bias, labels, logits, dlogits, st, B, K, NC, scale, use_smem);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -513,8 +546,7 @@ static int fc3_bwd_launch(const float* h, const float* w, const float* dl, float
   uint32_t thresh = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
   if (smem > 48 * 1024)
     DDL_CHECK_CUDA(cudaFuncSetAttribute(fc3_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  fc3_bwd_kernel<<<(K + 31) / 32, 256, smem, s>>>(h, w, dl, dw, db, dh, dbh, B, K, NC, seed, stream, thresh,
-                                                 keep_prob >= 1.f ? 1.f : 1.f / keep_prob, st);
+  DDL_LAUNCH(fc3_bwd_kernel, (K + 31) / 32, 256, smem, s, h, w, dl, dw, db, dh, dbh, B, K, NC, seed, stream, thresh, keep_prob >= 1.f ? 1.f : 1.f / keep_prob, st);
   DDL_LAUNCH_CHECK();
   return 0;
 }
@@ -531,7 +563,7 @@ int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, f
 }
 
 int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int B, int NC, cudaStream_t s) {
-  accuracy_kernel<<<(B + 127) / 128, 128, 0, s>>>(logits, labels, correct, B, NC);
+  DDL_LAUNCH(accuracy_kernel, (B + 127) / 128, 128, 0, s, logits, labels, correct, B, NC);
   DDL_LAUNCH_CHECK();
   return 0;
 }

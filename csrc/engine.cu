@@ -96,6 +96,17 @@ void pick_tiling(int pix_tiles, int nout, int kiters, bool allow_split, int* nti
   *ntile = nt; *ksplit = ks;
 }
 
+// FC layers (one pixel tile, M <= 128 rows): the work is streaming the weight matrix once, so spread it
+// over ~a wave of SMs with narrow N tiles and a cluster split over K (the fused epilogue survives).
+void pick_fc_tiling(int nout, int kiters, int* ntile, int* ksplit) {
+  const int nt = 32;
+  const int ctas = cdiv(nout, nt);
+  int ks = ctas >= 120 ? 1 : (128 + ctas - 1) / ctas;
+  if (ks > 8) ks = 8;
+  while (ks > 1 && kiters / ks < 2) --ks;
+  *ntile = nt; *ksplit = ks;
+}
+
 int pix_tiles_of(DdlTcPlan* pl) {
   int info[8];
   ddl_tc_plan_info(pl, info);
@@ -119,18 +130,23 @@ int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
     out->conv[l - 1] = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, nt, ks, 0,
                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!out->conv[l - 1]) return -1;
-    out->conv_split[l - 1] = ks;
+    out->conv_split[l - 1] = ddl_tc_plan_needs_zero(out->conv[l - 1]) ? 2 : 1;   // > 1: raw must be zeroed
   }
   const float* fc_in = e->nconv ? e->pooled[3] : nullptr;   // mlp: x itself (bound at run time)
   const int vf = 2 * e->nconv;
   const float kp = train ? c.keep_prob : 1.f;
   const int drop = (train && c.keep_prob < 1.f) ? 4 : 0;
+  int fnt, fks;
   if (e->nconv) {
-    out->fc[0] = ddl_tc_plan_act(0, fc_in, (train && c.fc_w_src[0]) ? c.fc_w_src[0] : e->P(vf), e->h1, B, 1, 1, e->F[0], e->F[1], 1, 32, 1, 1 | 2 | drop,
+    pick_fc_tiling(e->F[1], cdiv(e->F[0], 32), &fnt, &fks);
+    if (B > 128) fks = 1;                      // evaluation batches already fill the machine with pixel tiles
+    out->fc[0] = ddl_tc_plan_act(0, fc_in, (train && c.fc_w_src[0]) ? c.fc_w_src[0] : e->P(vf), e->h1, B, 1, 1, e->F[0], e->F[1], 1, fnt, fks, 1 | 2 | drop,
                                  e->P(vf + 1), nullptr, 1.f, train ? c.st : nullptr, 0, kp, nullptr, train && c.fc_w_src[0] ? const_cast<float*>(e->P(vf)) : nullptr);
     if (!out->fc[0]) return -1;
   }
-  out->fc[1] = ddl_tc_plan_act(0, e->h1, (train && c.fc_w_src[1]) ? c.fc_w_src[1] : e->P(vf + 2), e->h2, B, 1, 1, e->F[1], e->F[2], 1, 32, 1, 1 | drop,
+  pick_fc_tiling(e->F[2], cdiv(e->F[1], 32), &fnt, &fks);
+  if (B > 128) fks = 1;
+  out->fc[1] = ddl_tc_plan_act(0, e->h1, (train && c.fc_w_src[1]) ? c.fc_w_src[1] : e->P(vf + 2), e->h2, B, 1, 1, e->F[1], e->F[2], 1, fnt, fks, 1 | drop,
                                e->P(vf + 3), nullptr, 1.f, train ? c.st : nullptr, 1, kp, nullptr, train && c.fc_w_src[1] ? const_cast<float*>(e->P(vf + 2)) : nullptr);
   if (!out->fc[1]) return -1;
   return 0;
@@ -144,12 +160,15 @@ int build_bwd(DdlEngine* e) {
   // fc2: dW2 = h1^T dh2 ; dh1 = (dh2 W2^T) * (h1 > 0) / keep
   e->wg_fc[1] = ddl_tc_plan_wgrad(e->dh2, e->h1, e->G(vf + 2), B, 1, 1, e->F[2], e->F[1], 1, 64, 1);
   // its epilogue also reduces the columns of dh1 into the fc1 bias gradient
-  e->dg_fc[1] = ddl_tc_plan_act(1, e->dh2, e->P(vf + 2), e->dh1, B, 1, 1, e->F[2], e->F[1], 1, 32, 1, 8, nullptr,
+  int fnt, fks;
+  pick_fc_tiling(e->F[1], cdiv(e->F[2], 32), &fnt, &fks);
+  e->dg_fc[1] = ddl_tc_plan_act(1, e->dh2, e->P(vf + 2), e->dh1, B, 1, 1, e->F[2], e->F[1], 1, fnt, fks, 8, nullptr,
                                 e->h1, inv_keep, nullptr, 0, 1.f, e->G(vf + 1), nullptr);
   if (!e->wg_fc[1] || !e->dg_fc[1]) return -1;
   if (e->nconv) {
     e->wg_fc[0] = ddl_tc_plan_wgrad(e->dh1, e->pooled[3], e->G(vf), B, 1, 1, e->F[1], e->F[0], 1, 64, 1);
-    e->dg_fc[0] = ddl_tc_plan_act(1, e->dh1, e->P(vf), e->dpool[3], B, 1, 1, e->F[1], e->F[0], 1, 32, 1, 0, nullptr,
+    pick_fc_tiling(e->F[0], cdiv(e->F[1], 32), &fnt, &fks);
+    e->dg_fc[0] = ddl_tc_plan_act(1, e->dh1, e->P(vf), e->dpool[3], B, 1, 1, e->F[1], e->F[0], 1, fnt, fks, 0, nullptr,
                                   nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!e->wg_fc[0] || !e->dg_fc[0]) return -1;
   }
@@ -169,7 +188,7 @@ int build_bwd(DdlEngine* e) {
     e->dg_conv[l - 1] = ddl_tc_plan_act(1, e->dfull[l], e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, nt, ks, 0,
                                         nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!e->dg_conv[l - 1]) return -1;
-    e->dg_split[l - 1] = ks;
+    e->dg_split[l - 1] = ddl_tc_plan_needs_zero(e->dg_conv[l - 1]) ? 2 : 1;
   }
   return 0;
 }
@@ -299,6 +318,8 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   if (ddl_tc_plan_run(e->dg_fc[1], s)) return -1;      // + fc1 bias gradient in its epilogue
   if (fork()) return -1;
   if (ddl_tc_plan_run(e->wg_fc[0], w)) return -1;
+  if (ddl_tc_plan_needs_zero(e->dg_fc[0]))             // plain split-K output: partial sums are red.add-ed
+    DDL_CHECK_CUDA(cudaMemsetAsync(e->dpool[3], 0, (size_t)B * e->F[0] * sizeof(float), s));
   if (ddl_tc_plan_run(e->dg_fc[0], s)) return -1;
   int v = 6;
   for (int l = 3; l >= 1; --l, v -= 2) {           // conv4, conv3, conv2

@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "../include/ddl_b200.h"
 #include <stdarg.h>
+#include <stdlib.h>
 
 namespace ddl {
 static thread_local char g_err[1024] = "";
@@ -12,6 +13,10 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* get_error() { return g_err; }
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("DDL_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
 }  // namespace ddl
 
 extern "C" const char* ddl_last_error(void) { return ddl::get_error(); }

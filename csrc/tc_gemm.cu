@@ -47,6 +47,9 @@ struct ActParams {
   int stages;
   int b_mn_major;                  // 1: weights [tap][cred][nout] (fprop), 0: [tap][nout][cred] (dgrad)
   int flags;
+  int cluster;                     // > 1: the ksplit CTAs of a tile form a thread-block cluster; ranks 1.. park their
+                                   // partial accumulators in `scratch`, rank 0 adds them and runs the fused epilogue
+  float* scratch;                  // [tiles][cluster-1][ntile/4][128] float4 partial tiles (plan-owned)
   int pull;                        // K4: weight tiles come from another rank's arena (map_w on a peer pointer);
                                    // pixel-tile 0 CTAs write every tile through to the local arena (map_wst)
   int debug;                       // perf experiments only: 1 = skip MMA issue, 2 = skip TMA loads
@@ -109,6 +112,7 @@ __device__ __forceinline__ uint32_t tmem_cols_for(int n) {
 __global__ void __launch_bounds__(kThreadsTc, 1)
 tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_w,
                    const __grid_constant__ CUtensorMap map_wst, const ActParams p) {
+  pdl_launch_dependents();                 // the next kernel may start its prologue now
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int a_bytes = kTileM * 128;
@@ -126,6 +130,9 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const int k_end = min(p.kiters, k_begin + per);
   const int niter = max(0, k_end - k_begin);
   const uint32_t ncols = tmem_cols_for(p.ntile);
+  const bool creduce = p.cluster > 1;
+  const uint32_t crank = creduce ? cluster_ctarank() : 0u;
+  const int tile_lin = blockIdx.y * gridDim.x + blockIdx.x;
 
   // K4 write-through: one CTA per weight tile (the first pixel tile) persists what it pulled
   const bool store_through = p.pull && blockIdx.x == 0 && p.b_mn_major;
@@ -145,6 +152,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_addr;
+  pdl_wait();                              // everything above overlapped the previous kernel; its data is needed from here
 
   if (warp == 2 && store_through) {
     // ================= K4 store warp: smem weight tile -> local arena (TMA store), before its epilogue duty
@@ -240,13 +248,39 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     }
     if (niter == 0 && elect_one()) umma_commit(&bars->tmem_full);
     __syncwarp();
-  } else {
+  } else if (creduce && crank != 0) {
+    // ================= split-K peer (warps 2..5): park the partial accumulator for the cluster leader
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    if (lane == 0) mbar_wait(&bars->tmem_full, 0);
+    __syncwarp();
+    tc_fence_after();
+    float4* part = reinterpret_cast<float4*>(p.scratch) +
+                   ((size_t)(tile_lin * (p.cluster - 1) + (crank - 1)) * (p.ntile / 4)) * 128 + row;
+    for (int c0 = 0; c0 < p.ntile; c0 += 16) {
+      float v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      if (niter == 0) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 16; j += 4)       // [col/4][row]: a warp writes 512 contiguous bytes per store
+        __stcg(part + (size_t)((c0 + j) / 4) * 128, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
+    }
+    __threadfence();
+  }
+  if (creduce) {                             // every thread of every CTA of the cluster
+    cluster_arrive_release();
+    cluster_wait_acquire();
+  }
+  if (warp >= 2 && (!creduce || crank == 0)) {
     // ================= epilogue (warps 2..5) =================
     const int q = warp & 3;                      // TMEM lane quarter this warp may read
     const int row = q * 32 + lane;
     const int rw = row % p.bw, rh = (row / p.bw) % p.bh, rn = row / (p.bw * p.bh);
     const int pw = w0 + rw, phh = h0 + rh, pn = n0 + rn;
-    const bool valid = (rn < p.bn) && pw < p.W && phh < p.H && pn < p.N && niter > 0;
+    const bool valid = (rn < p.bn) && pw < p.W && phh < p.H && pn < p.N && (niter > 0 || creduce);
     const int64_t pix = ((int64_t)pn * p.H + phh) * p.W + pw;
     float* orow = p.out + pix * p.nout + nt0;
     const float* mrow = (p.flags & EPI_MASKPOS) ? p.mask_act + pix * p.nout + nt0 : nullptr;
@@ -255,9 +289,25 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     if (lane == 0) mbar_wait(&bars->tmem_full, 0);      // one poller per warp: 128 threads hammering the
     __syncwarp();                                        // same mbarrier slow the producer / MMA handoffs
     tc_fence_after();
+    const float4* parts = creduce ? reinterpret_cast<const float4*>(p.scratch) +
+                                        ((size_t)(tile_lin * (p.cluster - 1)) * (p.ntile / 4)) * 128 + row
+                                  : nullptr;
     for (int c0 = 0; c0 < p.ntile; c0 += 16) {
       float v[16];
       tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      if (creduce) {                         // add the peers' partial tiles (L2-resident, coalesced)
+        if (niter == 0) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = 0.f;
+        }
+        for (int r = 0; r < p.cluster - 1; ++r) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            const float4 t = __ldcg(parts + ((size_t)r * (p.ntile / 4) + (c0 + j) / 4) * 128);
+            v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
+          }
+        }
+      }
       if (p.flags & EPI_ATOMIC) {
         if (valid) {
 #pragma unroll
@@ -327,6 +377,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
 __global__ void __launch_bounds__(kThreadsTc, 1)
 tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_x,
                 const WgradParams p) {
+  pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int R = p.bw * p.bh * p.bn;
@@ -364,6 +415,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_addr;
+  pdl_wait();                              // everything above overlapped the previous kernel; its data is needed from here
 
   if (warp == 0) {
     const uint32_t tx = (uint32_t)((a_live + ntap * b_live) * box_bytes);
@@ -539,6 +591,7 @@ struct DdlTcPlan {
   int kind;                 // 0 act, 1 wgrad
   CUtensorMap map_a, map_b;
   CUtensorMap map_c;        // act plans with K4 pull: store map of the local weight copy (else = map_b)
+  float* scratch = nullptr; // cluster split-K partial tiles (owned)
   ActParams act;
   WgradParams wg;
   dim3 grid;
@@ -569,7 +622,21 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
   p.ksplit = ksplit < 1 ? 1 : (ksplit > p.kiters ? p.kiters : ksplit);
   p.nout = nout; p.ntile = ntile;
   p.b_mn_major = dgrad ? 0 : 1;
-  p.flags = flags | (p.ksplit > 1 ? EPI_ATOMIC : 0);
+  // Split-K reduction, two ways (measured, profiles/launches_step_r1_d.csv):
+  //  * plain outputs (conv fprop / dgrad: bias+ReLU live in the pool kernel) - red.add into a zeroed
+  //    `out`; every CTA flushes its own tile in parallel.  17.8 us for conv4 fprop at ksplit 11;
+  //  * outputs with a fused epilogue (FC layers: bias / ReLU / dropout / mask / column sums) - the ksplit
+  //    (<= 8) CTAs of a tile form a thread-block cluster; ranks 1.. park partial tiles in plan-owned,
+  //    L2-resident scratch, one cluster barrier, rank 0 adds them and runs the epilogue.  Keeps the
+  //    fusion and needs no zeroing, but rank 0 alone reads (ksplit-1) tiles: 44.5 us for the same conv4
+  //    case, so it is only used where the tile is narrow (N tile 32) and the epilogue must stay fused.
+  const bool fused_epi = (flags & (EPI_BIAS | EPI_RELU | EPI_DROPOUT | EPI_MASKPOS)) != 0 || colsum != nullptr;
+  const bool want_cluster = getenv("DDL_TC_NO_CLUSTER") == nullptr &&
+                            (fused_epi || getenv("DDL_TC_FORCE_CLUSTER") != nullptr);
+  if (want_cluster && p.ksplit > 8) p.ksplit = 8;
+  p.cluster = (want_cluster && p.ksplit > 1) ? p.ksplit : 1;
+  p.scratch = nullptr;
+  p.flags = flags | ((p.ksplit > 1 && p.cluster == 1) ? EPI_ATOMIC : 0);
   p.pull = (w_store_dst != nullptr && !dgrad && w_store_dst != w) ? 1 : 0;
   p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
   p.trace = nullptr;
@@ -595,9 +662,14 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
   p.stages = stages;
   pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
   pl->grid = dim3(p.tiles_w * p.tiles_h * p.tiles_n, ceil_div(nout, ntile), p.ksplit);
+  if (p.cluster > 1) {
+    const size_t bytes = (size_t)pl->grid.x * pl->grid.y * (p.cluster - 1) * kTileM * ntile * sizeof(float);
+    if (cudaMalloc((void**)&pl->scratch, bytes) != cudaSuccess) { delete pl; return fail("cudaMalloc(split-K scratch) failed"); }
+    p.scratch = pl->scratch;
+  }
   const uint64_t da[4] = {(uint64_t)cred, (uint64_t)W, (uint64_t)H, (uint64_t)N};
   const uint32_t ba[4] = {kKB, (uint32_t)p.bw, (uint32_t)p.bh, (uint32_t)p.bn};
-  if (make_map4(&pl->map_a, act, da, ba, false)) { delete pl; return nullptr; }
+  if (make_map4(&pl->map_a, act, da, ba, false)) { ddl_tc_plan_destroy(pl); return nullptr; }
   const int taps = ksize * ksize;
   if (!dgrad) {           // W as [taps][cred][nout]: inner = nout
     const uint64_t dw[4] = {(uint64_t)nout, (uint64_t)cred, (uint64_t)taps, 1};
@@ -685,15 +757,24 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
 
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s) {
   DDL_REQUIRE(pl != nullptr, "ddl_tc_plan_run: null plan");
-  if (pl->kind == 0)
-    tc_act_gemm_kernel<<<pl->grid, kThreadsTc, pl->smem, s>>>(pl->map_a, pl->map_b, pl->map_c, pl->act);
+  if (pl->kind == 0 && pl->act.cluster > 1) {
+    DDL_CHECK_CUDA(ddl::launch(tc_act_gemm_kernel, pl->grid, dim3(kThreadsTc), pl->smem, s, (unsigned)pl->act.cluster,
+                               pl->map_a, pl->map_b, pl->map_c, pl->act));
+  } else if (pl->kind == 0)
+    DDL_LAUNCH(tc_act_gemm_kernel, pl->grid, kThreadsTc, pl->smem, s, pl->map_a, pl->map_b, pl->map_c, pl->act);
   else
-    tc_wgrad_kernel<<<pl->grid, kThreadsTc, pl->smem, s>>>(pl->map_a, pl->map_b, pl->wg);
+    DDL_LAUNCH(tc_wgrad_kernel, pl->grid, kThreadsTc, pl->smem, s, pl->map_a, pl->map_b, pl->wg);
   DDL_LAUNCH_CHECK();
   return 0;
 }
 
-void ddl_tc_plan_destroy(DdlTcPlan* pl) { delete pl; }
+void ddl_tc_plan_destroy(DdlTcPlan* pl) {
+  if (pl && pl->scratch) cudaFree(pl->scratch);
+  delete pl;
+}
+
+/* 1 when the plan accumulates with red.add and `out` must therefore be zeroed before every run */
+int ddl_tc_plan_needs_zero(const DdlTcPlan* pl) { return pl && pl->kind == 0 && (pl->act.flags & EPI_ATOMIC) ? 1 : 0; }
 
 /* perf experiments: copies the clock64 trace of an act plan created under DDL_TC_TRACE=1 */
 int ddl_tc_plan_trace(const DdlTcPlan* pl, unsigned long long* host_out, int n) {
@@ -788,7 +869,7 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
   p.nout = cout; p.ntile = ntile;
   p.b_mn_major = 1;
   p.flags = ksplit > 1 ? EPI_ATOMIC : 0;
-  p.pull = 0; p.debug = 0; p.trace = nullptr;
+  p.pull = 0; p.debug = 0; p.trace = nullptr; p.cluster = 1; p.scratch = nullptr;
   p.out = raw; p.bias = nullptr; p.colsum = nullptr; p.mask_act = nullptr; p.mask_scale = 1.f;
   p.st = nullptr; p.drop_stream_off = 0; p.drop_thresh24 = 1u << 24; p.drop_inv_keep = 1.f;
   const int stage_bytes = kTileM * 128 + ntile * 128;
@@ -809,7 +890,7 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
   // split-K partial sums are added with red.add, so the region must start at zero; the array still
   // holds whatever the previous call left there
   if (ksplit > 1) DDL_CHECK_CUDA(cudaMemsetAsync(raw, 0, need, s));
-  tc_act_gemm_kernel<<<pl.grid, kThreadsTc, pl.smem, s>>>(pl.map_a, pl.map_b, pl.map_b, pl.act);
+  DDL_LAUNCH(tc_act_gemm_kernel, pl.grid, kThreadsTc, pl.smem, s, pl.map_a, pl.map_b, pl.map_b, pl.act);
   DDL_LAUNCH_CHECK();
   return ddl_maxpool_fwd(raw, bias, y, idx, N, H, W, cout, s);
 }

@@ -74,14 +74,15 @@ def conv5x5_wgrad(dy: torch.Tensor, x: torch.Tensor, ksize: int = 5, ntile: int 
 
 
 def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
-               dropout: Optional[Tuple[torch.Tensor, int, float]] = None, ntile: int = 32) -> torch.Tensor:
+               dropout: Optional[Tuple[torch.Tensor, int, float]] = None, ntile: int = 32,
+               ksplit: int = 1) -> torch.Tensor:
     """tf.matmul(x, w) + b [+ relu] [+ dropout] (model.py:70-82).  dropout = (step_state, stream_off, keep)."""
     B, K = x.shape
     N = w.shape[1]
     out = torch.empty(B, N, device=x.device, dtype=torch.float32)
     flags = (EPI_BIAS if bias is not None else 0) | (EPI_RELU if relu else 0) | (EPI_DROPOUT if dropout else 0)
     st, off, keep = dropout if dropout else (None, 0, 1.0)
-    plan = native.lib().ddl_tc_plan_act(0, native.ptr(x), native.ptr(w), native.ptr(out), B, 1, 1, K, N, 1, ntile, 1,
+    plan = native.lib().ddl_tc_plan_act(0, native.ptr(x), native.ptr(w), native.ptr(out), B, 1, 1, K, N, 1, ntile, ksplit,
                                         flags, native.ptr(bias), None, 1.0, native.ptr(st), off, keep, None, None)
     _run_plan(plan)
     return out

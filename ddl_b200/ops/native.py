@@ -107,6 +107,7 @@ def lib() -> C.CDLL:
         "ddl_tc_plan_run": ([vp, vp], i32),
         "ddl_tc_plan_destroy": ([vp], None),
         "ddl_tc_plan_info": ([vp, C.POINTER(C.c_int)], i32),
+        "ddl_tc_plan_needs_zero": ([vp], i32),
         "ddl_dev_malloc": ([C.POINTER(vp), C.c_size_t], i32),
         "ddl_dev_free": ([vp], i32),
         "ddl_ipc_export": ([vp, vp], i32),

@@ -83,7 +83,9 @@ int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int 
  *   act plan, dgrad=1: out[pix,n] = epi(sum_{tap,c} act[pix-off(tap), c] * w[tap][n][c])
  *   wgrad plan:        out[tap][b][a] += sum_pix g[pix,a] * x[pix+off(tap), b]
  * flags: 1 bias, 2 relu, 4 dropout (seed/stream from st), 8 multiply by (mask_act > 0) * mask_scale.
- * ksplit > 1 accumulates raw sums with red.add into a pre-zeroed out (no bias/relu/dropout).
+ * ksplit > 1 without epilogue flags: raw partial sums are added with red.add into a pre-zeroed out
+ * (ddl_tc_plan_needs_zero() returns 1).  ksplit in [2,8] WITH epilogue flags / colsum: the split CTAs of a
+ * tile form a thread-block cluster and reduce through plan-owned scratch, keeping the fused epilogue.
  * colsum (may be NULL): += per-column sums of the final output values (a bias gradient).
  * w_store_dst (may be NULL; fprop only) - K4, the pull fused into the consumer GEMM: `w` may then point
  * into ANOTHER rank's parameter arena (a peer-mapped pointer): the weight tiles are TMA-loaded over
@@ -100,6 +102,7 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);
 void ddl_tc_plan_destroy(DdlTcPlan* pl);
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8);
+int ddl_tc_plan_needs_zero(const DdlTcPlan* pl);
 
 /* ---- allocation-free convolution block (csrc/tc_gemm.cu).  No counterpart in the reference. --------
  * For host programs that must not call cudaMalloc: ones that have given the whole device to another

@@ -104,7 +104,9 @@ def test_tc_conv_fprop(H, Cin, Cout, B):
     assert rel_err(out, ref) < TF32_TOL
     out32 = K.conv5x5_fprop(x, w, ntile=32)
     assert rel_err(out32, ref) < TF32_TOL
-    outs = K.conv5x5_fprop(x, w, ntile=32, ksplit=3)
+    outs = K.conv5x5_fprop(x, w, ntile=32, ksplit=3)          # split-K, red.add into a zeroed output
+    assert rel_err(outs, ref) < TF32_TOL
+    outs = K.conv5x5_fprop(x, w, ksplit=8)
     assert rel_err(outs, ref) < TF32_TOL
 
 
@@ -141,6 +143,9 @@ def test_tc_linear_fwd_dx_dw(B, Kin, N):
     assert rel_err(out, ref.float()) < TF32_TOL
     out = K.linear_fwd(x, w, b, relu=True)
     assert rel_err(out, ref.float().relu()) < TF32_TOL
+    if Kin >= 256:                                            # fused epilogue behind a cluster split over K
+        out = K.linear_fwd(x, w, b, relu=True, ksplit=4)
+        assert rel_err(out, ref.float().relu()) < TF32_TOL
     dy = torch.randn(B, N, device=dev())
     dx = K.linear_dx(dy, w)
     assert rel_err(dx, (dy.double() @ w.double().t()).float()) < TF32_TOL
