@@ -206,6 +206,8 @@ def main() -> int:
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t[0].item())
+    if hasattr(tr.transport, "finish"):
+        tr.transport.finish()                 # async: drain accumulators, final pull
     acc = tr.evaluate()
     stats = tr.transport.stats() if hasattr(tr.transport, "stats") else {}
     tr.close()

@@ -113,6 +113,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1)
 tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_w,
                    const __grid_constant__ CUtensorMap map_wst, const ActParams p) {
   pdl_launch_dependents();                 // the next kernel may start its prologue now
+  const bool ptrace = (p.debug & 16) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0;
+  if (ptrace && threadIdx.x == 0) p.trace[0] = ddl_globaltimer();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int a_bytes = kTileM * 128;
@@ -152,7 +154,9 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_addr;
+  if (ptrace && threadIdx.x == 0) p.trace[1] = ddl_globaltimer();
   pdl_wait();                              // everything above overlapped the previous kernel; its data is needed from here
+  if (ptrace && threadIdx.x == 0) p.trace[2] = ddl_globaltimer();
 
   if (warp == 2 && store_through) {
     // ================= K4 store warp: smem weight tile -> local arena (TMA store), before its epilogue duty
@@ -191,7 +195,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
       mbar_wait(&bars->empty[s], ph ^ 1u);
       if (elect_one()) {
         if (ptr) p.trace[i * 4 + 1] = clock64();
-        if (!(p.debug & 8) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512) p.trace[i * 4 + 0] = clock64();
+        if (!(p.debug & 24) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512) p.trace[i * 4 + 0] = clock64();
         int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
         if (p.flip) { dh = -dh; dw = -dw; }
         uint8_t* sa = smem + (size_t)s * stage_bytes;
@@ -222,9 +226,10 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     int s = 0;
     uint32_t ph = 0;
     for (int i = 0; i < niter; ++i) {
-      const bool tr = !(p.debug & 8) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512 && lane == 0;
+      const bool tr = !(p.debug & 24) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512 && lane == 0;
       if (tr) p.trace[i * 4 + 1] = clock64();
       mbar_wait(&bars->full[s], ph);
+      if (ptrace && lane == 0 && i == 0) p.trace[3] = ddl_globaltimer();
       if (tr) p.trace[i * 4 + 2] = clock64();
       tc_fence_after();
       if (elect_one()) {
@@ -241,6 +246,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
         }
         umma_commit(&bars->empty[s]);            // smem slot reusable once these MMAs have read it
         if (i == niter - 1) umma_commit(&bars->tmem_full);   // accumulator complete
+        if (ptrace && i == niter - 1) p.trace[4] = ddl_globaltimer();
       }
       __syncwarp();
       if (tr) p.trace[i * 4 + 3] = clock64();
@@ -270,10 +276,12 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     }
     __threadfence();
   }
+  if (ptrace && threadIdx.x == 64) p.trace[5] = ddl_globaltimer();
   if (creduce) {                             // every thread of every CTA of the cluster
     cluster_arrive_release();
     cluster_wait_acquire();
   }
+  if (ptrace && threadIdx.x == 64) p.trace[6] = ddl_globaltimer();
   if (warp >= 2 && (!creduce || crank == 0)) {
     // ================= epilogue (warps 2..5) =================
     const int q = warp & 3;                      // TMEM lane quarter this warp may read
@@ -288,13 +296,20 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     if (p.flags & EPI_DROPOUT) { seed = p.st->seed; stream = p.st->stream + p.drop_stream_off; }
     if (lane == 0) mbar_wait(&bars->tmem_full, 0);      // one poller per warp: 128 threads hammering the
     __syncwarp();                                        // same mbarrier slow the producer / MMA handoffs
+    if (ptrace && threadIdx.x == 64) p.trace[7] = ddl_globaltimer();
     tc_fence_after();
     const float4* parts = creduce ? reinterpret_cast<const float4*>(p.scratch) +
                                         ((size_t)(tile_lin * (p.cluster - 1)) * (p.ntile / 4)) * 128 + row
                                   : nullptr;
     for (int c0 = 0; c0 < p.ntile; c0 += 16) {
       float v[16];
-      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      if (p.debug & 64) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = (float)j;
+      } else {
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      }
+      if (ptrace && threadIdx.x == 64 && c0 == 0) p.trace[10] = ddl_globaltimer();
       if (creduce) {                         // add the peers' partial tiles (L2-resident, coalesced)
         if (niter == 0) {
 #pragma unroll
@@ -350,18 +365,22 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
           if (lane == j && nt0 + c0 + j < p.nout) atomicAdd(p.colsum + nt0 + c0 + j, sv);
         }
       }
-      if (valid) {
+      if (ptrace && threadIdx.x == 64 && c0 == 0) p.trace[11] = ddl_globaltimer();
+      if (valid && !(p.debug & 32)) {
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
           if (nt0 + c0 + j < p.nout)
             *reinterpret_cast<float4*>(orow + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
         }
       }
+      if (ptrace && threadIdx.x == 64 && c0 == 0) p.trace[12] = ddl_globaltimer();
     }
   }
+  if (ptrace && threadIdx.x == 64) p.trace[8] = ddl_globaltimer();
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, ncols);
+  if (ptrace && threadIdx.x == 32) p.trace[9] = ddl_globaltimer();
 }
 
 // ------------------------------------------------------------------------------------------------
