@@ -37,8 +37,8 @@ def _digest() -> str:
     h = hashlib.sha256()
     for path in sources() + [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cuh", ".h"))] \
             + [os.path.join(ROOT, "include", "ddl_b200.h")]:
-        with open(path, "rb") as f:
-            h.update(path.encode() + b"\0" + f.read())
+        with open(path, "rb") as f:             # relative names: the stamp must survive a move of the tree
+            h.update(os.path.relpath(path, ROOT).encode() + b"\0" + f.read())
     h.update(" ".join(NVCC_FLAGS).encode())
     return h.hexdigest()
 
@@ -59,7 +59,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     logs = {}
 
     def compile_one(src):
-        obj = os.path.join(OBJDIR, os.path.basename(src)[:-3] + ".o")
+        obj = os.path.join(OBJDIR, "%s.%d.o" % (os.path.basename(src)[:-3], os.getpid()))
         cmd = [exe] + NVCC_FLAGS + ["-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         logs[src] = r.stdout + r.stderr
@@ -69,12 +69,20 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=min(8, len(sources()))) as ex:
         objs = list(ex.map(compile_one, sources()))
-    link = [exe, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
+    tmp = "%s.tmp.%d" % (LIB, os.getpid())        # link aside, then rename: concurrent ranks never see a torn .so
+    link = [exe, "-shared", "-o", tmp] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(link, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
-    with open(LIB + ".sha256", "w") as f:
+    os.replace(tmp, LIB)
+    for o in objs:
+        try:
+            os.remove(o)
+        except OSError:
+            pass
+    with open(LIB + ".sha256.tmp.%d" % os.getpid(), "w") as f:
         f.write(_digest())
+    os.replace(LIB + ".sha256.tmp.%d" % os.getpid(), LIB + ".sha256")
     with open(os.path.join(ROOT, "build", "ptxas.log"), "w") as f:
         for src, log in logs.items():
             f.write("==== %s\n%s\n" % (os.path.relpath(src, ROOT), log))
