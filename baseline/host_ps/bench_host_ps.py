@@ -17,7 +17,7 @@ import tempfile
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def run(a) -> int:
+def run(a, emit=lambda o: print(json.dumps(o))) -> int:
     if int(os.environ.get("RANK", "0")) != 0:
         return 0                                   # under torchrun only rank 0 drives the MPMD job
     from ddl_b200.parallel.launch import launch
@@ -34,18 +34,18 @@ def run(a) -> int:
         finally:
             os.environ.update(env_keep)
         if rc != 0:
-            print(json.dumps({"impl": "host_ps", "error": "launcher exited with %d" % rc}))
+            emit({"impl": "host_ps", "error": "launcher exited with %d" % rc})
             return rc
         rows = []
         for f in glob.glob(mpath + "*"):
             rows += [json.loads(l) for l in open(f) if "steady_samples_per_s" in l]
     slow = max(r["steady_s"] for r in rows)
     steady_steps = rows[0]["steady_steps"]
-    print(json.dumps({
+    emit({
         "metric": "samples/sec", "value": steady_steps * a.batch_size * n / slow, "unit": "samples/s", "n_gpus": n,
         "steps": steady_steps, "warmup": 3, "ms_per_step": slow * 1e3 / steady_steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (torch ops, TF32 off)", "impl": "host_ps",
         "data": "synthetic MNIST-shaped", "timing": "host wall clock, max over workers (transport is host-side)",
         "config": {"model": "mnist_cnn_14var", "variant": a.variant, "global_batch": a.batch_size * n,
-                   "parallelism": "ps%d(cpu)+w%d(gpu), host/gloo transport" % (n, n)}}))
+                   "parallelism": "ps%d(cpu)+w%d(gpu), host/gloo transport" % (n, n)}})
     return 0

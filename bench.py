@@ -95,12 +95,21 @@ def parse():
 
 def main() -> int:
     a = parse()
+    # stdout carries exactly ONE line (the JSON): libraries that print banners there (NCCL's version line,
+    # torchrun children) are redirected to stderr for the duration of the run.
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj) -> None:
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(obj) + "\n").encode())
+
     if a.impl == "reference":
-        print(json.dumps({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE}))
+        emit({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE})
         return 0
     if a.impl == "host_ps":
         from baseline.host_ps.bench_host_ps import run as run_host
-        return run_host(a)
+        return run_host(a, emit)
 
     import torch
     import torch.distributed as dist
@@ -116,6 +125,7 @@ def main() -> int:
             # convenience: re-launch ourselves under torch.distributed.run
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(a.gpus),
                    "--master-addr", "127.0.0.1", "--master-port", "29531", os.path.abspath(__file__)] + sys.argv[1:]
+            os.dup2(real_stdout, 1)           # the children do their own redirection
             return subprocess.call(cmd)
         raise SystemExit("WORLD_SIZE=%d does not match --gpus %d" % (world, a.gpus))
     if not torch.cuda.is_available():
@@ -237,7 +247,7 @@ def main() -> int:
             "final_loss": losses[-1] if losses else None, "first_loss": losses[0] if losses else None,
             "test_accuracy_after_bench": acc, "transport_stats": stats,
         }
-        print(json.dumps(out))
+        emit(out)
     return 0
 
 
