@@ -109,13 +109,17 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
   const int64_t n4 = (a.end - a.begin) / 4;
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = a.begin + q * 4;
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-    for (int w = 0; w < c.world; ++w) {
-      if (!((a.worker_mask >> w) & 1u)) continue;
-      const float4 x = ldcg4(c.grads[w] + i);       // peer load over NVLink (L2 of the peer)
-      g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+    // all peer loads first (each is a ~2 us NVLink round trip), then a fixed-order sum: W loads in flight
+    // instead of W dependent round trips, and the result is still bitwise reproducible
+    float4 x[DDL_MAX_PEERS];
+#pragma unroll
+    for (int w = 0; w < DDL_MAX_PEERS; ++w) {
+      x[w] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (w < c.world && ((a.worker_mask >> w) & 1u)) x[w] = ldcg4(c.grads[w] + i);
     }
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int w = 0; w < DDL_MAX_PEERS; ++w) { g.x += x[w].x; g.y += x[w].y; g.z += x[w].z; g.w += x[w].w; }
     g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
     const float4 pn = opt_apply<KIND>(*reinterpret_cast<float4*>(myp + i), g, a.m, a.v, i, step, a.a, a.b, a.eps);
     *reinterpret_cast<float4*>(myp + i) = pn;

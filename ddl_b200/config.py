@@ -75,7 +75,9 @@ class Config:
     quirk_parity: bool = False      # reproduce Q1/Q2 gradient-sum bugs (off: true sum)
     device: str = "auto"            # auto | cpu | cuda
     graphs: bool = True             # capture the step in a CUDA graph when possible
-    fused_pull_gemm: bool = True    # K4: FC weights consumed straight from owner shards
+    fused_pull_gemm: bool = False   # K4: fc1/fc2 forward GEMMs TMA-load their weights straight from the owner's
+                                    # arena (pull fused into the consumer).  Off by default: measured slower than
+                                    # the store-based pull fused into the update kernel
     timeout_s: float = 120.0        # collective / rendezvous timeout (failure detection)
     log_time: bool = True           # print the reference's "Time:" line
 
@@ -155,7 +157,8 @@ def build_parser(role: str = "worker") -> argparse.ArgumentParser:
     p.add_argument("--quirk-parity", action="store_true")
     p.add_argument("--device", choices=("auto", "cpu", "cuda"), default=_env_default("device", d.device))
     p.add_argument("--no-graphs", dest="graphs", action="store_false", default=True)
-    p.add_argument("--no-fused-pull-gemm", dest="fused_pull_gemm", action="store_false", default=True)
+    p.add_argument("--fused-pull-gemm", dest="fused_pull_gemm", action="store_true",
+                   default=_env_default("fused_pull_gemm", False))
     p.add_argument("--timeout-s", type=float, default=_env_default("timeout_s", d.timeout_s))
     return p
 

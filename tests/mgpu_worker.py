@@ -26,13 +26,13 @@ def base_cfg(**kw):
     return Config(**d).validate()
 
 
-def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd"):
+def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd", k4=True):
     """Training loop through the engine: every worker holds bitwise-identical parameters after each
     sync step, owners' ranges are the source of truth, the CUDA-graph path is taken."""
     P = world if layout_kind == "colocated" else 1
     W = world if layout_kind == "colocated" else world - 1
     cfg = base_cfg(mode="sync", shard=shard if P > 1 else "none", num_ps=P, num_workers=W, transport="fused",
-                   graphs=graphs, variant="mnist_sync_sharding_greedy", optimizer=opt)
+                   graphs=graphs, variant="mnist_sync_sharding_greedy", optimizer=opt, fused_pull_gemm=k4)
     tr = SPMDTrainer(cfg, rank, world, rank, layout_kind)
     nb = 5
     for i in range(nb):
@@ -48,7 +48,7 @@ def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd"):
             assert torch.equal(allp[tr.layout.owner_rank(sh)][b:e], allp[wr[0]][b:e]), "owner range mismatch"
     st = tr.transport.stats()
     assert st["optimizer_steps"] == nb, st
-    if shard != "flat" and world > 1:
+    if k4 and shard != "flat" and world > 1:
         # K4 is live: the fc1 / fc2 forward GEMMs of non-owner workers read the owner's arena (peer pointer)
         assert len(tr.transport.k4_src) == 2
         if tr.layout.is_worker and layout_kind == "dedicated":
@@ -147,6 +147,7 @@ def main():
     if case == "sync_colocated":
         case_sync(rank, world, "colocated", "greedy", graphs=False)
         case_sync(rank, world, "colocated", "flat", graphs=True, opt="adam")
+        case_sync(rank, world, "colocated", "greedy", graphs=True, opt="adam", k4=False)
     elif case == "sync_dedicated":
         case_sync(rank, world, "dedicated", "none", graphs=True, opt="adam")
     elif case == "sync_vs_nccl":
