@@ -433,6 +433,122 @@ __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restr
   }
 }
 
+// fc3 forward + softmax cross-entropy + fc3 backward in ONE kernel (training path).
+// Every block recomputes the [B, NC] logits (B*K*NC MACs - tiny) so no grid-wide hand-off is needed
+// between "dlogits ready" and the weight / input gradients; block b then owns the 32 k-columns
+// [32b, 32b+32) exactly like fc3_bwd_kernel.  Block 0 alone accumulates the loss / accuracy.
+__global__ void __launch_bounds__(256) fc3_fused_kernel(const float* __restrict__ h, const float* __restrict__ w,
+                                                        const float* __restrict__ bias, const int* __restrict__ labels,
+                                                        float* __restrict__ dw, float* __restrict__ db,
+                                                        float* __restrict__ dh, float* __restrict__ dbh,
+                                                        DdlStepState* st, int B, int K, int NC, float scale,
+                                                        uint32_t stream_off, uint32_t thresh24, float inv_keep) {
+  pdl_enter();
+  extern __shared__ float sm[];
+  __shared__ float colred[8][32];
+  float* sw3 = sm;                        // [K][NC]
+  float* sdl = sw3 + K * NC;              // [B][NC]
+  float* sh = sdl + B * NC;               // [B][32]
+  const int k0 = blockIdx.x * 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const uint32_t seed = st->seed, stream = st->stream + stream_off;
+  for (int i = threadIdx.x; i < K * NC; i += blockDim.x) sw3[i] = w[i];
+  for (int i = threadIdx.x; i < B * 32; i += blockDim.x) {
+    const int r = i >> 5, k = k0 + (i & 31);
+    sh[i] = (k < K) ? h[(int64_t)r * K + k] : 0.f;
+  }
+  __syncthreads();
+  // ---- phase 1: logits, softmax, dlogits for every row (warp per row)
+  float loss_acc = 0.f;
+  unsigned correct_acc = 0;
+  for (int row = warp; row < B; row += nwarps) {
+    float acc[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) acc[c] = 0.f;
+    for (int kb = 0; kb < K; kb += 32 * 8) {
+      float hv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int k = kb + u * 32 + lane;
+        hv[u] = k < K ? h[(int64_t)row * K + k] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int k = kb + u * 32 + lane;
+        if (k < K) {
+          const float* wr = sw3 + k * NC;
+#pragma unroll
+          for (int c = 0; c < 16; ++c)
+            if (c < NC) acc[c] += hv[u] * wr[c];
+        }
+      }
+    }
+    float z = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      float v = acc[c];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == c && c < NC) z = v + bias[c];
+    }
+    float mx = z;
+    int am = lane;
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+      if (om > mx || (om == mx && oa < am)) { mx = om; am = oa; }
+    }
+    const float e = (lane < NC) ? __expf(z - mx) : 0.f;
+    float se = e;
+    for (int o = 16; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+    const int lab = labels[row];
+    if (lane < NC) sdl[row * NC + lane] = (e / se - (lane == lab ? 1.f : 0.f)) * scale;
+    const float zl = __shfl_sync(0xffffffffu, z, lab);
+    if (lane == 0) { loss_acc += logf(se) + mx - zl; correct_acc += (am == lab) ? 1u : 0u; }
+  }
+  if (blockIdx.x == 0 && lane == 0) {
+    atomicAdd(&st->loss_sum, loss_acc);
+    if (correct_acc) atomicAdd(&st->correct, correct_acc);
+  }
+  __syncthreads();
+  // ---- phase 2: dW[k, c], db[c], dh[r, k] (+ column sums of dh = bias gradient of the previous layer)
+  const int c = lane, kk = warp;
+  if (c < NC) {
+    for (int ks = kk; ks < 32; ks += nwarps) {
+      const int k = k0 + ks;
+      if (k >= K) break;
+      float s2 = 0.f;
+      for (int r = 0; r < B; ++r) s2 += sh[r * 32 + ks] * sdl[r * NC + c];
+      dw[(int64_t)k * NC + c] += s2;
+    }
+    if (blockIdx.x == 0 && kk == 0) {
+      float s2 = 0.f;
+      for (int r = 0; r < B; ++r) s2 += sdl[r * NC + c];
+      db[c] += s2;
+    }
+  }
+  float colsum = 0.f;
+  for (int t = threadIdx.x; t < B * 32; t += blockDim.x) {
+    const int r = t >> 5, ks = t & 31, k = k0 + ks;
+    if (k >= K) continue;
+    float s2 = 0.f;
+    for (int cc = 0; cc < NC; ++cc) s2 += sdl[r * NC + cc] * sw3[k * NC + cc];
+    const uint32_t e = (uint32_t)(r * K + k);
+    const bool keep = thresh24 >= (1u << 24) || ddl_dropout_keep(seed, stream, e, thresh24);
+    const float o = keep ? s2 * inv_keep : 0.f;
+    dh[(int64_t)r * K + k] = o;
+    colsum += o;
+  }
+  if (dbh) {
+    colred[warp][lane] = colsum;
+    __syncthreads();
+    if (threadIdx.x < 32 && k0 + threadIdx.x < K) {
+      float t2 = 0.f;
+      for (int l = 0; l < nwarps; ++l) t2 += colred[l][threadIdx.x];
+      dbh[k0 + threadIdx.x] += t2;
+    }
+  }
+}
+
 __global__ void accuracy_kernel(const float* __restrict__ logits, const int* __restrict__ labels,
                                 unsigned* __restrict__ correct, int B, int NC) {
   pdl_enter();
@@ -560,6 +676,25 @@ int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, f
                    int B, int K, int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob,
                    cudaStream_t s) {
   return fc3_bwd_launch(h, w, dl, dw, db, dh, dbh, B, K, NC, 0, stream_off, st, keep_prob, s);
+}
+
+int ddl_fc3_fused_st(const float* h, const float* w, const float* bias, const int* labels, float* dw, float* db,
+                     float* dh, float* dbh, DdlStepState* st, int B, int K, int NC, float scale, uint32_t stream_off,
+                     float keep_prob, cudaStream_t s) {
+  DDL_REQUIRE(NC <= 16 && st != nullptr && labels != nullptr, "ddl_fc3_fused_st: NC <= 16, st and labels required");
+  const size_t smem = ((size_t)K * NC + (size_t)B * NC + (size_t)B * 32) * sizeof(float);
+  DDL_REQUIRE(smem <= 200 * 1024, "ddl_fc3_fused_st: K=%d, B=%d do not fit shared memory", K, B);
+  if (smem > 48 * 1024) {
+    static bool attr_done = false;
+    if (!attr_done) {
+      DDL_CHECK_CUDA(cudaFuncSetAttribute(fc3_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr_done = true;
+    }
+  }
+  const uint32_t thresh = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
+  DDL_LAUNCH(fc3_fused_kernel, (K + 31) / 32, 256, smem, s, h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, scale,
+             stream_off, thresh, keep_prob >= 1.f ? 1.f : 1.f / keep_prob);
+  return 0;
 }
 
 int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int B, int NC, cudaStream_t s) {

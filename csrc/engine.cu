@@ -10,6 +10,7 @@
 #include "../include/ddl_b200.h"
 
 #include <map>
+#include <stdlib.h>
 #include <new>
 #include <vector>
 
@@ -297,12 +298,19 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   DDL_CHECK_CUDA(cudaMemsetAsync(c.grads, 0, (size_t)c.arena_elems * sizeof(float), s));
   if (forward(e, fp, x, B, true, s)) return -1;
   const int vf = 2 * e->nconv;
-  if (ddl_fc3_xent_fwd(e->h2, e->P(vf + 4), e->P(vf + 5), y, nullptr, e->dlogits, c.st, B, e->F[2], e->F[3],
-                       1.f / (float)B, s)) return -1;
-  // ---- backward
-  // fc3 backward also emits the fc2 bias gradient (column sums of dh2)
-  if (ddl_fc3_bwd_st(e->h2, e->P(vf + 4), e->dlogits, e->G(vf + 4), e->G(vf + 5), e->dh2, e->G(vf + 3), B, e->F[2],
-                     e->F[3], c.st, 1, c.keep_prob, s)) return -1;
+  // fc3 forward + loss + fc3 backward in one kernel; it also emits the fc2 bias gradient (column sums of dh2)
+  // (measured: the single-kernel version is 3x SLOWER - 112 us vs 15 + 22 us - because every block walks all
+  //  B rows with 8 warps instead of one warp per row across 13 blocks; kept behind DDL_FC3_FUSED for study)
+  static const bool fc3_fused = getenv("DDL_FC3_FUSED") != nullptr;
+  if (fc3_fused && (size_t)(e->F[2] * e->F[3] + B * (e->F[3] + 32)) * sizeof(float) <= 200 * 1024) {
+    if (ddl_fc3_fused_st(e->h2, e->P(vf + 4), e->P(vf + 5), y, e->G(vf + 4), e->G(vf + 5), e->dh2, e->G(vf + 3), c.st, B,
+                         e->F[2], e->F[3], 1.f / (float)B, 1, c.keep_prob, s)) return -1;
+  } else {
+    if (ddl_fc3_xent_fwd(e->h2, e->P(vf + 4), e->P(vf + 5), y, nullptr, e->dlogits, c.st, B, e->F[2], e->F[3],
+                         1.f / (float)B, s)) return -1;
+    if (ddl_fc3_bwd_st(e->h2, e->P(vf + 4), e->dlogits, e->G(vf + 4), e->G(vf + 5), e->dh2, e->G(vf + 3), B, e->F[2],
+                       e->F[3], c.st, 1, c.keep_prob, s)) return -1;
+  }
   // Main stream: the data-gradient chain.  Side stream: every weight-gradient GEMM, forked as soon as its
   // dY exists and joined once before the optimizer.
   cudaStream_t w = e->side;

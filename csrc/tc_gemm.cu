@@ -181,6 +181,31 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     __syncwarp();
   }
 
+  if (warp == 3 && !(p.debug & 2)) {
+    // ================= second TMA producer: the weight (B) boxes.  One UTMALDG of a 128-row box keeps the
+    // issuing lane busy for ~200 cycles, so A and B are issued from two warps in parallel; the transaction
+    // bytes of both are announced by warp 0's expect_tx (a complete_tx that lands first just drives the
+    // count negative until then - the phase cannot complete before warp 0's arrive).
+    int s = 0;
+    uint32_t ph = 0;
+    int tap = k_begin / p.cblocks, cb = k_begin % p.cblocks;
+    for (int i = 0; i < niter; ++i) {
+      mbar_wait(&bars->empty[s], ph ^ 1u);
+      if (elect_one()) {
+        uint8_t* sb = smem + (size_t)s * stage_bytes + a_bytes;
+        if (p.b_mn_major) {
+          for (int j = 0; j < p.ntile / 32; ++j)
+            tma_load_4d(sb + j * 4096, &map_w, &bars->full[s], nt0 + 32 * j, cb * kKB, tap, 0);
+        } else {
+          tma_load_4d(sb, &map_w, &bars->full[s], cb * kKB, nt0, tap, 0);
+        }
+      }
+      __syncwarp();
+      if (++cb == p.cblocks) { cb = 0; ++tap; }
+      if (++s == p.stages) { s = 0; ph ^= 1u; }
+    }
+  }
+
   if (warp == 0) {
     // ================= TMA producer (warp-uniform loop, one elected lane issues) =================
     const int box_rows = p.bw * p.bh * p.bn;
@@ -203,16 +228,10 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
         if (p.debug & 2) {
           mbar_arrive(&bars->full[s]);
         } else {
-          mbar_expect_tx(&bars->full[s], tx);
+          mbar_expect_tx(&bars->full[s], tx);      // covers the A box (here) and the B boxes (warp 3)
           if (ptr) p.trace[i * 4 + 2] = clock64();
           tma_load_4d(sa, &map_act, &bars->full[s], cb * kKB, w0 + dw, h0 + dh, n0);
           if (ptr) p.trace[i * 4 + 3] = clock64();
-          if (p.b_mn_major) {
-            for (int j = 0; j < p.ntile / 32; ++j)
-              tma_load_4d(sb + j * 4096, &map_w, &bars->full[s], nt0 + 32 * j, cb * kKB, tap, 0);
-          } else {
-            tma_load_4d(sb, &map_w, &bars->full[s], cb * kKB, nt0, tap, 0);
-          }
         }
       }
       __syncwarp();

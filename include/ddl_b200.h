@@ -73,6 +73,10 @@ int ddl_fc3_bwd(const float* h, const float* w, const float* dl, float* dw, floa
 int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, float* dbh,
                    int B, int K, int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob,
                    cudaStream_t s);
+/* training path: fc3 forward + softmax-xent + fc3 backward (+ fc2 bias gradient) in one launch */
+int ddl_fc3_fused_st(const float* h, const float* w, const float* bias, const int* labels, float* dw, float* db,
+                     float* dh, float* dbh, DdlStepState* st, int B, int K, int NC, float scale, uint32_t stream_off,
+                     float keep_prob, cudaStream_t s);
 int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int B, int NC, cudaStream_t s);
 
 /* ---- tcgen05 implicit-GEMM plans (csrc/tc_gemm.cu) ------------------------------------------
