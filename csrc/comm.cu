@@ -95,7 +95,8 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
   pdl_enter();
   __shared__ uint32_t s_last;
   const uint32_t t = a.st->t;                       // same on every rank: all ranks advance together
-  const uint32_t epochA = 2u * t + 1u, epochB = 2u * t + 2u;
+  const uint32_t nb = a.nbuckets > 1 ? (uint32_t)a.nbuckets : 1u;
+  const uint32_t epochA = 2u * nb * t + 2u * (uint32_t)a.bucket + 1u, epochB = epochA + 1u;
   // ---- barrier A: my gradients are complete (previous kernels on this stream) -> tell everyone
   if (blockIdx.x == 0) {
     __threadfence_system();
@@ -106,9 +107,12 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
 
   const float step = (KIND == 2) ? a.st->lr_t : a.lr;
   float* myp = c.params[c.rank];
-  const int64_t n4 = (a.end - a.begin) / 4;
+  const int nsub = a.nsub > 0 ? a.nsub : 1;
+  for (int sr = 0; sr < nsub; ++sr) {
+  const int64_t rb = a.nsub > 0 ? a.sub_begin[sr] : a.begin, re = a.nsub > 0 ? a.sub_end[sr] : a.end;
+  const int64_t n4 = (re - rb) / 4;
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t i = a.begin + q * 4;
+    const int64_t i = rb + q * 4;
     // all peer loads first (each is a ~2 us NVLink round trip), then a fixed-order sum: W loads in flight
     // instead of W dependent round trips, and the result is still bitwise reproducible
     float4 x[DDL_MAX_PEERS];
@@ -133,6 +137,7 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
         __stcg(reinterpret_cast<float4*>(c.params[d] + i), pn);   // peer store: the pull, fused
       }
     }
+  }
   }
   // ---- barrier B: last block to finish publishes "my range is delivered" and waits for the others.
   // One fence per block, not per thread: bar.sync makes the block's stores observed by thread 0, whose
@@ -315,7 +320,18 @@ int ddl_can_access_peer(int dev, int peer) {
 int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, cudaStream_t s) {
   DDL_REQUIRE(c->world >= 1 && c->world <= DDL_MAX_PEERS, "world %d out of range", c->world);
   DDL_REQUIRE(a->begin % 4 == 0 && a->end % 4 == 0, "shard range must be float4 aligned");
-  const int grid = comm_grid(a->end - a->begin);
+  DDL_REQUIRE(a->nsub >= 0 && a->nsub <= DDL_MAX_SUB, "nsub %d out of range", a->nsub);
+  int64_t elems = a->end - a->begin;
+  if (a->nsub > 0) {
+    elems = 0;
+    for (int i = 0; i < a->nsub; ++i) {
+      DDL_REQUIRE(a->sub_begin[i] % 4 == 0 && a->sub_end[i] % 4 == 0, "sub-range must be float4 aligned");
+      elems += a->sub_end[i] - a->sub_begin[i];
+    }
+  }
+  int grid = comm_grid(elems);
+  // a bucket that overlaps the backward spins on its barrier next to compute kernels: keep it narrow
+  if (a->nbuckets > 1 && a->bucket == 0 && grid > 148) grid = 148;
   if (kind == 0) DDL_LAUNCH(sync_push_update_pull_kernel<0>, grid, kCommThreads, 0, s, *c, *a);
   else if (kind == 1) DDL_LAUNCH(sync_push_update_pull_kernel<1>, grid, kCommThreads, 0, s, *c, *a);
   else DDL_LAUNCH(sync_push_update_pull_kernel<2>, grid, kCommThreads, 0, s, *c, *a);

@@ -63,9 +63,14 @@ struct DdlEngine {
   std::vector<void*> allocs;
   // fork/join: weight-gradient kernels run on a side stream next to the dgrad chain (they only feed the
   // optimizer); captured into the step graph as parallel branches
+  // backward-overlapped push (gradient bucketing): argument blocks of the bucket launched on the side stream
+  DdlComm ov_comm;
+  DdlSyncArgs ov_args[4];
+  int ov_n = 0, ov_kind = 2;
   cudaStream_t side = nullptr;
+  cudaStream_t side2 = nullptr;    // the overlapped push/update/pull bucket: must not delay the remaining wgrads
   cudaEvent_t ev_fork[8] = {};
-  cudaEvent_t ev_join = nullptr;
+  cudaEvent_t ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr;
 
   const float* P(int v) const { return cfg.params + cfg.var_offset[v]; }
   float* G(int v) const { return cfg.grads + cfg.var_offset[v]; }
@@ -259,6 +264,9 @@ DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg) {
   for (int l = 0; l < 4; ++l)
     if (alloc(e, (void**)&e->dfull[l], (size_t)cfg->batch * e->S[l] * e->S[l] * e->C[l + 1] * 4)) return fail(e, nullptr);
   if (cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking) != cudaSuccess) return fail(e, "side stream");
+  if (cudaStreamCreateWithFlags(&e->side2, cudaStreamNonBlocking) != cudaSuccess) return fail(e, "side stream 2");
+  if (cudaEventCreateWithFlags(&e->ev_fork2, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_join2, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   for (auto& ev : e->ev_fork)
     if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   if (cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
@@ -284,7 +292,10 @@ void ddl_engine_destroy(DdlEngine* e) {
   for (void* p : e->allocs) cudaFree(p);
   for (auto& ev : e->ev_fork) if (ev) cudaEventDestroy(ev);
   if (e->ev_join) cudaEventDestroy(e->ev_join);
+  if (e->ev_fork2) cudaEventDestroy(e->ev_fork2);
+  if (e->ev_join2) cudaEventDestroy(e->ev_join2);
   if (e->side) cudaStreamDestroy(e->side);
+  if (e->side2) cudaStreamDestroy(e->side2);
   delete e;
 }
 
@@ -337,12 +348,29 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     if (ddl_maxpool_bwd(e->dpool[l], e->idx[l], e->dfull[l], e->G(v + 1), B, S, S, cout, s)) return -1;
     if (fork()) return -1;
     if (ddl_tc_plan_run(e->wg_conv[l - 1], w)) return -1;
+    if (l == 2 && e->ov_n > 0) {                   // every gradient of conv3..fc3 is complete once stream w gets here
+      DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork2, w));
+      DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fork2, 0));
+      for (int i = 0; i < e->ov_n; ++i)
+        if (ddl_sync_push_update_pull(&e->ov_comm, &e->ov_args[i], e->ov_kind, e->side2)) return -1;
+      DDL_CHECK_CUDA(cudaEventRecord(e->ev_join2, e->side2));
+    }
     if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
   }
   if (ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull[0], nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
   if (ddl_conv1_wgrad(x, e->dfull[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
   DDL_CHECK_CUDA(cudaEventRecord(e->ev_join, w));
   DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join, 0));
+  if (e->ov_n > 0) DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join2, 0));
+  return 0;
+}
+
+int ddl_engine_set_overlap(DdlEngine* e, const DdlComm* c, const DdlSyncArgs* args, int nargs, int kind) {
+  DDL_REQUIRE(e != nullptr && nargs >= 0 && nargs <= 4, "ddl_engine_set_overlap: bad arguments");
+  if (nargs > 0) e->ov_comm = *c;
+  for (int i = 0; i < nargs; ++i) e->ov_args[i] = args[i];
+  e->ov_n = nargs;
+  e->ov_kind = kind;
   return 0;
 }
 

@@ -69,7 +69,7 @@ class NativeBackend:
         advanced (``advance_state``) by the caller."""
         native.check(self.L.ddl_engine_train_step(self.h, native.ptr(x), native.ptr(y), native.stream_ptr()),
                      "ddl_engine_train_step")
-        native.count(26)
+        native.count(26 + getattr(self, "overlap_launches", 0))    # 26 engine kernels (+ the overlapped push bucket)
 
     def advance_state(self, advance_opt: bool = True) -> None:
         c = self.cfg

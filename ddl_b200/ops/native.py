@@ -16,6 +16,7 @@ from . import build as _build
 
 MAX_PEERS = 16
 MAX_SKIP = 4
+MAX_SUB = 16
 STALE_BINS = 16
 PAD_SLOTS = 64
 PAD_PUSHES = 32
@@ -42,7 +43,9 @@ class SyncArgs(C.Structure):
                 ("st", C.c_void_p), ("done_counter", C.c_void_p), ("worker_mask", C.c_uint32),
                 ("dest_mask", C.c_uint32), ("lr", C.c_float), ("a", C.c_float), ("b", C.c_float),
                 ("eps", C.c_float), ("gscale", C.c_float),
-                ("skip_begin", C.c_int64 * MAX_SKIP), ("skip_end", C.c_int64 * MAX_SKIP)]
+                ("skip_begin", C.c_int64 * MAX_SKIP), ("skip_end", C.c_int64 * MAX_SKIP),
+                ("nsub", C.c_int), ("bucket", C.c_int), ("nbuckets", C.c_int),
+                ("sub_begin", C.c_int64 * MAX_SUB), ("sub_end", C.c_int64 * MAX_SUB)]
 
 
 class AsyncArgs(C.Structure):
@@ -123,6 +126,7 @@ def lib() -> C.CDLL:
         "ddl_engine_create": ([C.POINTER(EngineCfg)], vp),
         "ddl_engine_destroy": ([vp], None),
         "ddl_engine_train_step": ([vp, vp, vp, vp], i32),
+        "ddl_engine_set_overlap": ([vp, C.POINTER(Comm), vp, i32, i32], i32),
         "ddl_engine_eval": ([vp, vp, vp, i32, vp, vp, vp], i32),
         "ddl_engine_buffer": ([vp, i32], vp),
         "ddl_memcpy_async": ([vp, vp, C.c_size_t, vp], i32),

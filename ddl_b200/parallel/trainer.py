@@ -119,6 +119,8 @@ class SPMDTrainer:
         self.model = Model(self.spec, self.params, self.grads, cfg, step_state=getattr(self.transport, "st", None),
                            worker=lay.my_worker or 0, num_workers=lay.num_workers,
                            fc_w_src=getattr(self.transport, "k4_src", None)) if lay.is_worker else None
+        if self.model is not None and self.model.backend == "native" and hasattr(self.transport, "attach_engine"):
+            self.transport.attach_engine(self.model.impl)
         self.transport.initial_sync()
         if lay.is_worker:
             self.x_test = self.data.x_test.to(self.device)

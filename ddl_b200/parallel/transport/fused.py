@@ -140,39 +140,78 @@ class FusedTransport(SpmdTransport):
         self.worker_mask = 0
         for wr in lay.worker_ranks:
             self.worker_mask |= 1 << wr
-        # per-owned-shard argument blocks
-        self.sync_args: List[native.SyncArgs] = []
-        for r in lay.my_shards:
+        # per-owned-shard argument blocks.  With gradient bucketing every step is served by two launches:
+        # bucket 0 = conv3..fc3 (ready early in the backward; the engine launches it on its side stream),
+        # bucket 1 = conv1 / conv2 (after the backward).  Every rank launches both, in that order.
+        spec = params.spec
+        self.bucketed = bool(cfg.overlap_push and cfg.mode == "sync" and spec.kind == "cnn")
+        self.engine_overlap = False
+        kind_id, step0, aa, bb, eps = FlatOptimizer(torch.zeros(1), cfg.optimizer, cfg.lr, cfg.beta1, cfg.beta2,
+                                                    cfg.eps, cfg.momentum, use_native=False).hyper(1)
+
+        def make_args(begin: int, end: int, bucket: int, nbuckets: int, subs) -> native.SyncArgs:
             a = native.SyncArgs()
-            a.begin, a.end = self.plan.shard_range[r]
+            a.begin, a.end = begin, end
             a.m = self.m.data_ptr() if self.m is not None else None
             a.v = self.v.data_ptr() if self.v is not None else None
             a.st = self.st.data_ptr()
-            a.done_counter = self.scratch.data_ptr()
-            a.worker_mask = self.worker_mask
-            a.dest_mask = self.worker_mask
-            kind, step, aa, bb, eps = FlatOptimizer(torch.zeros(1), cfg.optimizer, cfg.lr, cfg.beta1, cfg.beta2,
-                                                    cfg.eps, cfg.momentum, use_native=False).hyper(1)
+            a.done_counter = self.scratch[4 * bucket:].data_ptr()
+            a.worker_mask = a.dest_mask = self.worker_mask
             a.lr, a.a, a.b, a.eps = cfg.lr, aa, bb, eps
             a.gscale = self.gscale if cfg.mode == "sync" else 1.0
             for k in range(native.MAX_SKIP):
                 a.skip_begin[k] = a.skip_end[k] = -1
-            self.sync_args.append(a)
-        if not self.sync_args:                       # worker-only rank: still takes part in the barriers
-            a = native.SyncArgs()
-            a.begin = a.end = 0
-            a.st = self.st.data_ptr()
-            a.done_counter = self.scratch.data_ptr()
-            a.worker_mask = a.dest_mask = self.worker_mask
-            for k in range(native.MAX_SKIP):
-                a.skip_begin[k] = a.skip_end[k] = -1
-            self.sync_args.append(a)
+            a.bucket, a.nbuckets = bucket, nbuckets
+            a.nsub = 0
+            if subs is not None:
+                a.nsub = len(subs)
+                for i, (sb, se) in enumerate(subs):
+                    a.sub_begin[i], a.sub_end[i] = sb, se
+                if not subs:                          # nothing of this bucket lives here: barrier-only launch
+                    a.nsub = 1
+                    a.sub_begin[0] = a.sub_end[0] = begin
+            return a
+
+        def bucket_subranges(begin: int, end: int, var_ids):
+            """Arena sub-ranges of [begin, end) covered by `var_ids` (alignment padding included), merged."""
+            from ..sharding import ALIGN_ELEMS
+            spans = []
+            for v in var_ids:
+                b = self.plan.var_offset[v]
+                e = b + (spec.vars[v].numel + ALIGN_ELEMS - 1) // ALIGN_ELEMS * ALIGN_ELEMS
+                b, e = max(b, begin), min(e, end)
+                if b < e:
+                    spans.append((b, e))
+            spans.sort()
+            merged = []
+            for b, e in spans:
+                if merged and merged[-1][1] == b:
+                    merged[-1] = (merged[-1][0], e)
+                else:
+                    merged.append((b, e))
+            return merged
+
+        early_vars, late_vars = list(range(4, spec.num_vars)), [0, 1, 2, 3]
+        self.sync_args: List[native.SyncArgs] = []        # launched by step()
+        self.early_args: List[native.SyncArgs] = []       # bucket 0 (engine side stream, or step() without engine)
+        ranges = [self.plan.shard_range[r] for r in lay.my_shards] or [(0, 0)]
+        for (b, e) in ranges:
+            if self.bucketed:
+                s0, s1 = bucket_subranges(b, e, early_vars), bucket_subranges(b, e, late_vars)
+                if len(s0) > native.MAX_SUB or len(s1) > native.MAX_SUB:
+                    self.bucketed = False
+            if self.bucketed:
+                self.early_args.append(make_args(b, e, 0, 2, s0))
+                self.sync_args.append(make_args(b, e, 1, 2, s1))
+            else:
+                self.sync_args.append(make_args(b, e, 0, 1, None))
+        if len(ranges) > 1:                               # single-process multi-shard: one launch per shard is fine
+            pass
         # ---- K4: variables whose pull is fused into their first consumer GEMM (fc1 / fc2 weights: each weight
         # byte is read exactly once per step by the [B<=128 x K] x [K x N] matmul, so fetching the tiles
         # straight from the owner over NVLink costs the same bytes as an all-gather and removes it).
         # Their owners do not broadcast those ranges; the consumer writes them through to its local arena.
         self.k4_src: Dict[int, Optional[int]] = {}
-        spec = params.spec
         if (cfg.fused_pull_gemm and cfg.mode == "sync" and lay.world > 1 and self.plan.policy != "flat"
                 and spec.kind == "cnn"):
             k = 0
@@ -182,7 +221,7 @@ class FusedTransport(SpmdTransport):
                 e = b + spec.vars[v].numel
                 self.k4_src[v] = None if owner_rank == lay.rank else mem["params"].ptrs[owner_rank] + 4 * b
                 if owner_rank == lay.rank:
-                    for a in self.sync_args:
+                    for a in self.sync_args + self.early_args:
                         if a.begin <= b and e <= a.end:
                             a.skip_begin[k], a.skip_end[k] = b, e
                 k += 1
@@ -236,8 +275,27 @@ class FusedTransport(SpmdTransport):
                                              1 if c.mode == "sync" else 0, self._s()), "ddl_step_advance")
         native.count()
 
-    def step(self) -> None:
+    def attach_engine(self, backend) -> None:
+        """Hand bucket 0 to the native engine: it launches those push/update/pull kernels on its side stream in
+        the middle of the backward (as soon as conv3..fc3 gradients exist), overlapping them with the conv2 /
+        conv1 backward - SURVEY 7.2 step 7, "backward-overlapped push"."""
+        if not (self.bucketed and self.early_args):
+            return
+        arr = (native.SyncArgs * len(self.early_args))(*self.early_args)
+        native.check(self.L.ddl_engine_set_overlap(backend.h, C.byref(self.comm), arr, len(self.early_args), self.kind),
+                     "ddl_engine_set_overlap")
+        self.engine_overlap = True
+        backend.overlap_launches = len(self.early_args)
+
+    def step(self, all_buckets: bool = False) -> None:
+        """push + update + pull of one step.  ``all_buckets`` also launches the bucket the engine normally
+        launches itself in the middle of the backward (transport-only tests, owner-only ranks)."""
         if self.cfg.mode == "sync":
+            if self.bucketed and (all_buckets or not self.engine_overlap):
+                for a in self.early_args:            # no engine on this rank (owner-only) or torch backend
+                    native.check(self.L.ddl_sync_push_update_pull(C.byref(self.comm), C.byref(a), self.kind, self._s()),
+                                 "ddl_sync_push_update_pull")
+                    native.count()
             for a in self.sync_args:
                 native.check(self.L.ddl_sync_push_update_pull(C.byref(self.comm), C.byref(a), self.kind, self._s()),
                              "ddl_sync_push_update_pull")

@@ -126,6 +126,7 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
 /* ---- peer-memory communication (csrc/comm.cu) -----------------------------------------------
  * Replaces the reference's mpi4py layer (SURVEY 2.3 call-site table). */
 #define DDL_MAX_SKIP 4
+#define DDL_MAX_SUB 16
 #define DDL_STALE_BINS 16
 /* signal pad layout (uint32 slots, one pad per rank) */
 #define DDL_PAD_BARRIER 16   /* [16,32): host-requested device barrier epochs, one slot per source */
@@ -150,6 +151,11 @@ typedef struct DdlSyncArgs {
   uint32_t dest_mask;              /* ranks that receive the updated range              */
   float lr, a, b, eps, gscale;
   int64_t skip_begin[DDL_MAX_SKIP], skip_end[DDL_MAX_SKIP];   /* not broadcast (K4 pulls them) */
+  /* Gradient bucketing (backward-overlapped push): a step may be served by `nbuckets` launches, each over
+   * `nsub` sub-ranges of [begin, end) (nsub == 0: the whole range).  Bucket b of step t uses barrier epochs
+   * 2*nbuckets*t + 2b + 1 / + 2, so every rank must launch the same buckets in the same order. */
+  int nsub, bucket, nbuckets;
+  int64_t sub_begin[DDL_MAX_SUB], sub_end[DDL_MAX_SUB];
 } DdlSyncArgs;
 
 typedef struct DdlAsyncArgs {
@@ -201,6 +207,10 @@ DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg);
 void ddl_engine_destroy(DdlEngine* e);
 /* sess.run(self.grads, keep_prob=.5) (mnist_sync/worker.py:30): x [B,784], y [B] class ids */
 int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream_t s);
+/* Backward-overlapped push: the engine launches ddl_sync_push_update_pull for these argument blocks on its
+ * side stream as soon as the gradients of conv3..fc3 (98% of the bytes) are complete, while the main stream
+ * still runs the conv2 / conv1 backward.  The caller launches the remaining bucket after the step. */
+int ddl_engine_set_overlap(DdlEngine* e, const DdlComm* c, const DdlSyncArgs* args, int nargs, int kind);
 /* sess.run(self.accuracy, keep_prob=1) (mnist_sync/worker.py:72) over n rows */
 int ddl_engine_eval(DdlEngine* e, const float* x, const int* y, int n, unsigned* correct, float* logits_out,
                     cudaStream_t s);

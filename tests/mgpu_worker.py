@@ -78,7 +78,10 @@ def case_sync_vs_nccl(rank, world, layout_kind, shard, opt):
             torch.cuda.synchronize()
             dist.barrier()
             tr.transport.begin_step()
-            tr.transport.step()
+            if transport == "fused":
+                tr.transport.step(all_buckets=True)     # no engine run here: launch its bucket too
+            else:
+                tr.transport.step()
             torch.cuda.synchronize()
             dist.barrier()
         if hasattr(tr.transport, "ensure_local"):
