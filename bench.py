@@ -89,6 +89,7 @@ def parse():
     ap.add_argument("--optimizer", default="adam")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--nvls", default="auto", choices=["auto", "on", "off"])
     ap.add_argument("--no-overlap", action="store_true", help="disable the backward-overlapped (bucketed) push")
     ap.add_argument("--k4", action="store_true", help="enable the pull fused into the fc1/fc2 GEMMs (K4)")
     ap.add_argument("--no-k4", action="store_true", help=argparse.SUPPRESS)
@@ -145,7 +146,7 @@ def main() -> int:
                  batch_size=a.batch_size, optimizer=a.optimizer, transport=transport, backend=backend,
                  synthetic=True, synthetic_train=max(6000, a.batch_size * 32), synthetic_test=1000, seed=1234,
                  eval_every=0, width_mult=a.width_mult, graphs=not a.no_graphs, log_time=False,
-                 fused_pull_gemm=a.k4 and not a.no_k4, overlap_push=not a.no_overlap).validate()
+                 fused_pull_gemm=a.k4 and not a.no_k4, overlap_push=not a.no_overlap, nvls=a.nvls).validate()
     kind = "colocated" if world > 1 else "auto"
     if world > 1 and num_ps == 1:
         kind = "colocated"

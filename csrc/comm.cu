@@ -113,17 +113,24 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
   const int64_t n4 = (re - rb) / 4;
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = rb + q * 4;
-    // all peer loads first (each is a ~2 us NVLink round trip), then a fixed-order sum: W loads in flight
-    // instead of W dependent round trips, and the result is still bitwise reproducible
-    float4 x[DDL_MAX_PEERS];
+    float4 g;
+    if (c.mc_grads != nullptr) {
+      // NVLS: the switch sums this offset of every rank's gradient arena (ranks that are not workers hold
+      // zeros) - one load, owner ingress 1x instead of Wx.  Summation order inside the switch is unspecified.
+      g = multimem_ld_reduce_add_v4(c.mc_grads + i);
+    } else {
+      // all peer loads first (each is a ~2 us NVLink round trip), then a fixed-order sum: W loads in flight
+      // instead of W dependent round trips, and the result is bitwise reproducible
+      float4 x[DDL_MAX_PEERS];
 #pragma unroll
-    for (int w = 0; w < DDL_MAX_PEERS; ++w) {
-      x[w] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (w < c.world && ((a.worker_mask >> w) & 1u)) x[w] = ldcg4(c.grads[w] + i);
+      for (int w = 0; w < DDL_MAX_PEERS; ++w) {
+        x[w] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (w < c.world && ((a.worker_mask >> w) & 1u)) x[w] = ldcg4(c.grads[w] + i);
+      }
+      g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int w = 0; w < DDL_MAX_PEERS; ++w) { g.x += x[w].x; g.y += x[w].y; g.z += x[w].z; g.w += x[w].w; }
     }
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-    for (int w = 0; w < DDL_MAX_PEERS; ++w) { g.x += x[w].x; g.y += x[w].y; g.z += x[w].z; g.w += x[w].w; }
     g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
     const float4 pn = opt_apply<KIND>(*reinterpret_cast<float4*>(myp + i), g, a.m, a.v, i, step, a.a, a.b, a.eps);
     *reinterpret_cast<float4*>(myp + i) = pn;
@@ -131,10 +138,14 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
 #pragma unroll
     for (int k = 0; k < DDL_MAX_SKIP; ++k) bcast = bcast && !(i >= a.skip_begin[k] && i < a.skip_end[k]);
     if (bcast) {
+      if (c.mc_params != nullptr) {
+        multimem_st_v4(c.mc_params + i, pn);      // NVLS: one store, the switch writes every rank's copy
+      } else {
 #pragma unroll 1
-      for (int d = 0; d < c.world; ++d) {
-        if (d == c.rank || !((a.dest_mask >> d) & 1u)) continue;
-        __stcg(reinterpret_cast<float4*>(c.params[d] + i), pn);   // peer store: the pull, fused
+        for (int d = 0; d < c.world; ++d) {
+          if (d == c.rank || !((a.dest_mask >> d) & 1u)) continue;
+          __stcg(reinterpret_cast<float4*>(c.params[d] + i), pn);   // peer store: the pull, fused
+        }
       }
     }
   }

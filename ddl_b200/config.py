@@ -78,6 +78,7 @@ class Config:
     fused_pull_gemm: bool = False   # K4: fc1/fc2 forward GEMMs TMA-load their weights straight from the owner's
                                     # arena (pull fused into the consumer).  Off by default: measured slower than
                                     # the store-based pull fused into the update kernel
+    nvls: str = "auto"              # auto | on | off: NVSwitch multicast (multimem.ld_reduce / multimem.st) for the sync push / pull
     overlap_push: bool = True       # sync + fused: push/update/pull conv3..fc3 (98% of the bytes) while conv2/conv1 backward runs
     timeout_s: float = 120.0        # collective / rendezvous timeout (failure detection)
     log_time: bool = True           # print the reference's "Time:" line
@@ -160,6 +161,7 @@ def build_parser(role: str = "worker") -> argparse.ArgumentParser:
     p.add_argument("--no-graphs", dest="graphs", action="store_false", default=True)
     p.add_argument("--fused-pull-gemm", dest="fused_pull_gemm", action="store_true",
                    default=_env_default("fused_pull_gemm", False))
+    p.add_argument("--nvls", choices=("auto", "on", "off"), default=_env_default("nvls", "auto"))
     p.add_argument("--no-overlap-push", dest="overlap_push", action="store_false", default=True)
     p.add_argument("--timeout-s", type=float, default=_env_default("timeout_s", d.timeout_s))
     return p

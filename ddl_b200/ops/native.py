@@ -35,7 +35,8 @@ assert C.sizeof(StepState) == 64
 class Comm(C.Structure):
     _fields_ = [("rank", C.c_int), ("world", C.c_int),
                 ("grads", C.c_void_p * MAX_PEERS), ("params", C.c_void_p * MAX_PEERS),
-                ("accum", C.c_void_p * MAX_PEERS), ("pads", C.c_void_p * MAX_PEERS)]
+                ("accum", C.c_void_p * MAX_PEERS), ("pads", C.c_void_p * MAX_PEERS),
+                ("mc_grads", C.c_void_p), ("mc_params", C.c_void_p)]
 
 
 class SyncArgs(C.Structure):

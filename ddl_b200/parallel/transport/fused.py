@@ -89,6 +89,49 @@ class SymmetricMemory:
             self.local = 0
 
 
+class MulticastMemory:
+    """Same contract as SymmetricMemory, allocated through torch's symmetric-memory allocator, which also
+    binds the buffers to an NVSwitch multicast object: ``mc`` is ONE device address naming the same offset
+    of every rank's buffer (NVLS).  Used for the parameter and gradient arenas of sync mode."""
+
+    def __init__(self, nbytes: int, rank: int, world: int, device: torch.device):
+        import torch.distributed._symmetric_memory as symm
+        self.rank, self.world, self.nbytes, self.device = rank, world, nbytes, device
+        self.t = symm.empty(nbytes // 4, dtype=torch.float32, device=device)
+        self.h = symm.rendezvous(self.t, dist.group.WORLD)
+        self.t.zero_()
+        self.local = self.t.data_ptr()
+        self.ptrs = [int(p) for p in self.h.buffer_ptrs]
+        self.mc = int(self.h.multicast_ptr or 0)
+        if self.ptrs[rank] != self.local:
+            raise native.NativeError("symmetric memory: local buffer pointer mismatch")
+
+    def tensor(self, dtype=torch.float32) -> torch.Tensor:
+        return self.t if dtype == torch.float32 else self.t.view(dtype)
+
+    def close(self) -> None:
+        self.h = None
+        self.t = None
+
+
+def _alloc_arena(nbytes: int, rank: int, world: int, device: torch.device, want_mc: str):
+    """Multicast-capable allocation when asked for (and possible), else plain cudaIpc peer mapping."""
+    if world > 1 and want_mc in ("auto", "on"):
+        try:
+            m = MulticastMemory(nbytes, rank, world, device)
+            ok = torch.tensor([1 if m.mc else 0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)       # all ranks or none
+            if int(ok.item()) == 1:
+                return m
+            m.close()
+        except Exception as e:                               # noqa: BLE001 - any failure means "no NVLS here"
+            if want_mc == "on":
+                raise native.NativeError("NVLS multicast requested but unavailable: %r" % (e,))
+        if want_mc == "on":
+            raise native.NativeError("NVLS multicast requested but this box exposes no multicast pointer")
+    return SymmetricMemory(nbytes, rank, world, device)
+
+
 class FusedTransport(SpmdTransport):
     name = "fused"
 
@@ -105,8 +148,9 @@ class FusedTransport(SpmdTransport):
                 if r != (device.index or 0) and r < world and not L.ddl_can_access_peer(device.index or 0, r):
                     raise native.NativeError("GPU %d cannot access GPU %d: no NVLink/P2P path" % (device.index or 0, r))
         nbytes = plan.total * 4
-        mem = {"params": SymmetricMemory(nbytes, layout.rank, world, device),
-               "grads": SymmetricMemory(nbytes, layout.rank, world, device),
+        want_mc = cfg.nvls if cfg.mode == "sync" else "off"
+        mem = {"params": _alloc_arena(nbytes, layout.rank, world, device, want_mc),
+               "grads": _alloc_arena(nbytes, layout.rank, world, device, want_mc),
                "pad": SymmetricMemory(native.PAD_SLOTS * 4, layout.rank, world, device)}
         if cfg.mode == "async":
             mem["accum"] = SymmetricMemory(nbytes, layout.rank, world, device)
@@ -137,6 +181,9 @@ class FusedTransport(SpmdTransport):
             self.comm.params[r] = mem["params"].ptrs[r]
             self.comm.pads[r] = mem["pad"].ptrs[r]
             self.comm.accum[r] = mem["accum"].ptrs[r] if "accum" in mem else None
+        self.nvls = bool(getattr(mem["grads"], "mc", 0) and getattr(mem["params"], "mc", 0))
+        self.comm.mc_grads = mem["grads"].mc if self.nvls else None
+        self.comm.mc_params = mem["params"].mc if self.nvls else None
         self.worker_mask = 0
         for wr in lay.worker_ranks:
             self.worker_mask |= 1 << wr
@@ -360,7 +407,7 @@ class FusedTransport(SpmdTransport):
 
     def stats(self) -> Dict[str, object]:
         s = native.read_step_state(self.st)
-        out = {"optimizer_steps": s["t"], "worker_steps": s["wstep"]}
+        out = {"optimizer_steps": s["t"], "worker_steps": s["wstep"], "nvls": getattr(self, "nvls", False)}
         if self.cfg.mode == "async":
             out["staleness_hist"] = self.stale_hist.cpu().tolist()
             pad = self.mem["pad"].tensor(torch.int32).cpu()

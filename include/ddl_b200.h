@@ -140,6 +140,11 @@ typedef struct DdlComm {
   float* params[DDL_MAX_PEERS];    /* every rank's parameter arena                */
   float* accum[DDL_MAX_PEERS];     /* every rank's async gradient accumulator     */
   uint32_t* pads[DDL_MAX_PEERS];   /* every rank's signal pad                     */
+  /* NVLS (NVSwitch multicast) views, NULL when unavailable: one address that names the SAME offset of every
+   * rank's arena.  multimem.ld_reduce on mc_grads returns the in-switch sum over all ranks (owner ingress
+   * 1x instead of Wx); multimem.st on mc_params writes every rank's copy at once (owner egress 1x). */
+  float* mc_grads;
+  float* mc_params;
 } DdlComm;
 
 typedef struct DdlSyncArgs {

@@ -26,13 +26,13 @@ def base_cfg(**kw):
     return Config(**d).validate()
 
 
-def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd", k4=True):
+def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd", k4=True, nvls="auto"):
     """Training loop through the engine: every worker holds bitwise-identical parameters after each
     sync step, owners' ranges are the source of truth, the CUDA-graph path is taken."""
     P = world if layout_kind == "colocated" else 1
     W = world if layout_kind == "colocated" else world - 1
     cfg = base_cfg(mode="sync", shard=shard if P > 1 else "none", num_ps=P, num_workers=W, transport="fused",
-                   graphs=graphs, variant="mnist_sync_sharding_greedy", optimizer=opt, fused_pull_gemm=k4)
+                   graphs=graphs, variant="mnist_sync_sharding_greedy", optimizer=opt, fused_pull_gemm=k4, nvls=nvls)
     tr = SPMDTrainer(cfg, rank, world, rank, layout_kind)
     nb = 5
     for i in range(nb):
@@ -59,7 +59,7 @@ def case_sync(rank, world, layout_kind, shard, graphs, opt="sgd", k4=True):
     dist.barrier()
 
 
-def case_sync_vs_nccl(rank, world, layout_kind, shard, opt):
+def case_sync_vs_nccl(rank, world, layout_kind, shard, opt, nvls="auto"):
     """The fused K1+K3 kernel against reduce + optimizer + broadcast done with NCCL, on IDENTICAL
     gradients (the engine's red.add-ordered sums are not run-to-run reproducible, and a ULP can flip a
     ReLU / pool arg-max, so end-to-end training runs are only statistically comparable)."""
@@ -68,7 +68,7 @@ def case_sync_vs_nccl(rank, world, layout_kind, shard, opt):
     results = {}
     for transport in ("fused", "nccl"):
         cfg = base_cfg(mode="sync", shard=shard if P > 1 else "none", num_ps=P, num_workers=W, transport=transport,
-                       variant="mnist_sync_sharding_greedy", optimizer=opt, lr=0.01, reduce="mean", graphs=False)
+                       variant="mnist_sync_sharding_greedy", optimizer=opt, lr=0.01, reduce="mean", graphs=False, nvls=nvls)
         tr = SPMDTrainer(cfg, rank, world, rank, layout_kind)
         for k in range(3):
             gen = torch.Generator(device="cuda").manual_seed(100 * k + rank)
@@ -157,6 +157,10 @@ def main():
         case_sync_vs_nccl(rank, world, "colocated", "greedy", "adam")
         case_sync_vs_nccl(rank, world, "colocated", "flat", "momentum")
         case_sync_vs_nccl(rank, world, "dedicated", "none", "sgd")
+    elif case == "sync_nvls_off":
+        os.environ["DDL_NVLS"] = "off"
+        case_sync(rank, world, "colocated", "greedy", graphs=True, opt="adam", k4=False, nvls="off")
+        case_sync_vs_nccl(rank, world, "colocated", "block", "adam", nvls="off")
     elif case == "async_sgd":
         case_async_counting(rank, world, "sgd")
     elif case == "async_adam":
