@@ -58,12 +58,16 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append([c.strip() for c in line.split(",")] + [time.time()])
 
-    def stop(self):
+    def stop(self, t_begin: float = 0.0, t_end: float = 1e18):
+        """Median SM clock / reasons over the samples that arrived inside [t_begin, t_end] (the timed regions);
+        nvidia-smi is started long before, because its own start-up takes longer than a short timed region."""
         if self.proc:
-            time.sleep(0.12)
+            time.sleep(0.05)
             self.proc.terminate()
+        inside = [r for r in self.rows if len(r) >= 9 and t_begin <= r[-1] <= t_end + 0.05]
+        self.rows = inside if inside else self.rows[-3:]
         sm = sorted(int(float(r[1])) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit())
         mx = [int(float(r[2])) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
         reasons = set()
@@ -150,6 +154,11 @@ def main() -> int:
     kind = "colocated" if world > 1 else "auto"
     if world > 1 and num_ps == 1:
         kind = "colocated"
+    # nvidia-smi sampler (every 20 ms) is started before anything else: it needs up to a second to produce its
+    # first row on an 8-GPU box, longer than a short timed region
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     tr = SPMDTrainer(cfg, rank, world, local, kind)
     dev = tr.device
     B = cfg.batch_size
@@ -165,12 +174,7 @@ def main() -> int:
     for i in range(max(3, a.warmup)):
         tr.train_step(i % nb)
     sync_all()
-    # clocks are sampled (nvidia-smi, every 20 ms) from here to the end of the e2e loop: both timed regions
-    sampler = ClockSampler(dev.index or 0)
-    sampler.start()
-    for i in range(8):                      # a few more untimed steps so the first sample already sees load
-        tr.train_step(i % nb)
-    sync_all()
+    t_load_begin = time.time()              # clock samples from here to the end of the e2e loop are reported
     graph_mode = tr._graph is not None
     launches_per_step = getattr(tr, "launches_per_step", None)
 
@@ -222,7 +226,7 @@ def main() -> int:
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t[0].item())
-    clocks = sampler.stop()
+    clocks = sampler.stop(t_load_begin, time.time())
     if hasattr(tr.transport, "finish"):
         tr.transport.finish()                 # async: drain accumulators, final pull
     acc = tr.evaluate()
