@@ -23,6 +23,7 @@
 #include "common.cuh"
 #include "../include/ddl_b200.h"
 #include <string.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -53,35 +54,41 @@ DDL_DEVICE void pad_wait(const DdlComm& c, uint32_t base, uint32_t epoch) {
   }
 }
 
+// optimizer arithmetic on registers: returns the new parameters, updates mv / vv in place
 template <int KIND>
-DDL_DEVICE float4 opt_apply(float4 pv, float4 gv, float* m, float* v, int64_t i, float step, float a, float b,
-                            float eps) {
+DDL_DEVICE float4 opt_math(float4 pv, float4 gv, float4& mv, float4& vv, float step, float a, float b, float eps) {
   float pp[4] = {pv.x, pv.y, pv.z, pv.w};
   float gg[4] = {gv.x, gv.y, gv.z, gv.w};
-  if (KIND == 0) {
+  float mm[4] = {mv.x, mv.y, mv.z, mv.w};
+  float vs[4] = {vv.x, vv.y, vv.z, vv.w};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) pp[k] -= step * gg[k];
-  } else if (KIND == 1) {
-    float4 mv = *reinterpret_cast<float4*>(m + i);
-    float mm[4] = {mv.x, mv.y, mv.z, mv.w};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { mm[k] = a * mm[k] + gg[k]; pp[k] -= step * mm[k]; }
-    *reinterpret_cast<float4*>(m + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-  } else {
-    float4 mv = *reinterpret_cast<float4*>(m + i);
-    float4 vv = *reinterpret_cast<float4*>(v + i);
-    float mm[4] = {mv.x, mv.y, mv.z, mv.w};
-    float vs[4] = {vv.x, vv.y, vv.z, vv.w};
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
+  for (int k = 0; k < 4; ++k) {
+    if (KIND == 0) {
+      pp[k] -= step * gg[k];
+    } else if (KIND == 1) {
+      mm[k] = a * mm[k] + gg[k];
+      pp[k] -= step * mm[k];
+    } else {
       mm[k] = a * mm[k] + (1.f - a) * gg[k];
       vs[k] = b * vs[k] + (1.f - b) * gg[k] * gg[k];
       pp[k] -= step * mm[k] / (sqrtf(vs[k]) + eps);
     }
-    *reinterpret_cast<float4*>(m + i) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-    *reinterpret_cast<float4*>(v + i) = make_float4(vs[0], vs[1], vs[2], vs[3]);
   }
+  mv = make_float4(mm[0], mm[1], mm[2], mm[3]);
+  vv = make_float4(vs[0], vs[1], vs[2], vs[3]);
   return make_float4(pp[0], pp[1], pp[2], pp[3]);
+}
+
+template <int KIND>
+DDL_DEVICE float4 opt_apply(float4 pv, float4 gv, float* m, float* v, int64_t i, float step, float a, float b,
+                            float eps) {
+  float4 mv = make_float4(0.f, 0.f, 0.f, 0.f), vv = mv;
+  if (KIND >= 1) mv = *reinterpret_cast<float4*>(m + i);
+  if (KIND == 2) vv = *reinterpret_cast<float4*>(v + i);
+  const float4 pn = opt_math<KIND>(pv, gv, mv, vv, step, a, b, eps);
+  if (KIND >= 1) *reinterpret_cast<float4*>(m + i) = mv;
+  if (KIND == 2) *reinterpret_cast<float4*>(v + i) = vv;
+  return pn;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -89,7 +96,10 @@ DDL_DEVICE float4 opt_apply(float4 pv, float4 gv, float* m, float* v, int64_t i,
 // m / v are indexed like the arena (only [begin, end) is touched).  `skip` lists arena ranges whose
 // new values are NOT broadcast because their first consumer GEMM pulls them itself (K4).
 // ------------------------------------------------------------------------------------------------
-template <int KIND>
+// U float4 per thread per trip: every load of a trip is issued before the first use, so a thread keeps
+// U x (workers) NVLink round trips (~2 us each) in flight.  U = 1 for latency-bound small ranges (more SMs, one
+// trip), U = 4 for bandwidth-bound large ones.
+template <int KIND, int U>
 __global__ void __launch_bounds__(kCommThreads)
 sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
   pdl_enter();
@@ -105,46 +115,86 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
   pad_wait(c, 0, epochA);                           // every block polls its own (local) pad
   __syncthreads();
 
+  constexpr int WCH = (U == 1) ? DDL_MAX_PEERS : 4;  // peers loaded per batch: WCH * U float4 in flight
   const float step = (KIND == 2) ? a.st->lr_t : a.lr;
   float* myp = c.params[c.rank];
   const int nsub = a.nsub > 0 ? a.nsub : 1;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int sr = 0; sr < nsub; ++sr) {
   const int64_t rb = a.nsub > 0 ? a.sub_begin[sr] : a.begin, re = a.nsub > 0 ? a.sub_end[sr] : a.end;
   const int64_t n4 = (re - rb) / 4;
-  for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t i = rb + q * 4;
-    float4 g;
+  for (int64_t q0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * U) {
+    float4 g[U];
     if (c.mc_grads != nullptr) {
       // NVLS: the switch sums this offset of every rank's gradient arena (ranks that are not workers hold
       // zeros) - one load, owner ingress 1x instead of Wx.  Summation order inside the switch is unspecified.
-      g = multimem_ld_reduce_add_v4(c.mc_grads + i);
-    } else {
-      // all peer loads first (each is a ~2 us NVLink round trip), then a fixed-order sum: W loads in flight
-      // instead of W dependent round trips, and the result is bitwise reproducible
-      float4 x[DDL_MAX_PEERS];
 #pragma unroll
-      for (int w = 0; w < DDL_MAX_PEERS; ++w) {
-        x[w] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (w < c.world && ((a.worker_mask >> w) & 1u)) x[w] = ldcg4(c.grads[w] + i);
+      for (int u = 0; u < U; ++u) {
+        const int64_t q = q0 + u * stride;
+        g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (q < n4) g[u] = multimem_ld_reduce_add_v4(c.mc_grads + rb + q * 4);
       }
-      g = make_float4(0.f, 0.f, 0.f, 0.f);
+    } else {
+      // all peer loads of a batch first, then a fixed-order sum (ascending rank): loads overlap instead of
+      // W dependent round trips, and the result is bitwise reproducible
 #pragma unroll
-      for (int w = 0; w < DDL_MAX_PEERS; ++w) { g.x += x[w].x; g.y += x[w].y; g.z += x[w].z; g.w += x[w].w; }
+      for (int u = 0; u < U; ++u) g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int w0 = 0; w0 < c.world; w0 += WCH) {
+        float4 x[WCH][U];
+#pragma unroll
+        for (int wi = 0; wi < WCH; ++wi) {
+          const int w = w0 + wi;
+          const bool on = w < c.world && ((a.worker_mask >> w) & 1u);
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t q = q0 + u * stride;
+            x[wi][u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (on && q < n4) x[wi][u] = ldcg4(c.grads[w] + rb + q * 4);
+          }
+        }
+#pragma unroll
+        for (int wi = 0; wi < WCH; ++wi) {
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            g[u].x += x[wi][u].x; g[u].y += x[wi][u].y; g[u].z += x[wi][u].z; g[u].w += x[wi][u].w;
+          }
+        }
+      }
     }
-    g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
-    const float4 pn = opt_apply<KIND>(*reinterpret_cast<float4*>(myp + i), g, a.m, a.v, i, step, a.a, a.b, a.eps);
-    *reinterpret_cast<float4*>(myp + i) = pn;
-    bool bcast = true;
+    // optimizer state of all U chunks is loaded before the first store (m / v / p may alias for the compiler)
+    float4 pv[U], mv[U], vv[U];
 #pragma unroll
-    for (int k = 0; k < DDL_MAX_SKIP; ++k) bcast = bcast && !(i >= a.skip_begin[k] && i < a.skip_end[k]);
-    if (bcast) {
-      if (c.mc_params != nullptr) {
-        multimem_st_v4(c.mc_params + i, pn);      // NVLS: one store, the switch writes every rank's copy
-      } else {
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = q0 + u * stride;
+      const int64_t i = rb + (q < n4 ? q : q0) * 4;
+      pv[u] = *reinterpret_cast<const float4*>(myp + i);
+      mv[u] = vv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (KIND >= 1) mv[u] = *reinterpret_cast<const float4*>(a.m + i);
+      if (KIND == 2) vv[u] = *reinterpret_cast<const float4*>(a.v + i);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = q0 + u * stride;
+      if (q >= n4) continue;
+      const int64_t i = rb + q * 4;
+      float4 gs = g[u];
+      gs.x *= a.gscale; gs.y *= a.gscale; gs.z *= a.gscale; gs.w *= a.gscale;
+      const float4 pn = opt_math<KIND>(pv[u], gs, mv[u], vv[u], step, a.a, a.b, a.eps);
+      if (KIND >= 1) *reinterpret_cast<float4*>(a.m + i) = mv[u];
+      if (KIND == 2) *reinterpret_cast<float4*>(a.v + i) = vv[u];
+      *reinterpret_cast<float4*>(myp + i) = pn;
+      bool bcast = true;
+#pragma unroll
+      for (int k = 0; k < DDL_MAX_SKIP; ++k) bcast = bcast && !(i >= a.skip_begin[k] && i < a.skip_end[k]);
+      if (bcast) {
+        if (c.mc_params != nullptr) {
+          multimem_st_v4(c.mc_params + i, pn);      // NVLS: one store, the switch writes every rank's copy
+        } else {
 #pragma unroll 1
-        for (int d = 0; d < c.world; ++d) {
-          if (d == c.rank || !((a.dest_mask >> d) & 1u)) continue;
-          __stcg(reinterpret_cast<float4*>(c.params[d] + i), pn);   // peer store: the pull, fused
+          for (int d = 0; d < c.world; ++d) {
+            if (d == c.rank || !((a.dest_mask >> d) & 1u)) continue;
+            __stcg(reinterpret_cast<float4*>(c.params[d] + i), pn);   // peer store: the pull, fused
+          }
         }
       }
     }
@@ -273,9 +323,14 @@ pull_allgather_kernel(const DdlComm c, const DdlAsyncArgs a) {
     if (owner == c.rank) continue;
     const float* src = c.params[owner];
     const int64_t b = a.shard_begin[o], n4 = (a.shard_end[o] - b) / 4;
-    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
-      const int64_t i = b + q * 4;
-      *reinterpret_cast<float4*>(myp + i) = ldcg4(src + i);
+    // 4 peer loads in flight per thread per trip
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t q0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q0 < n4; q0 += 4 * stride) {
+      float4 x[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (q0 + u * stride < n4) x[u] = ldcg4(src + b + (q0 + u * stride) * 4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (q0 + u * stride < n4) *reinterpret_cast<float4*>(myp + b + (q0 + u * stride) * 4) = x[u];
     }
   }
 }
@@ -342,10 +397,21 @@ int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, 
   }
   int grid = comm_grid(elems);
   // a bucket that overlaps the backward spins on its barrier next to compute kernels: keep it narrow
-  if (a->nbuckets > 1 && a->bucket == 0 && grid > 148) grid = 148;
-  if (kind == 0) DDL_LAUNCH(sync_push_update_pull_kernel<0>, grid, kCommThreads, 0, s, *c, *a);
-  else if (kind == 1) DDL_LAUNCH(sync_push_update_pull_kernel<1>, grid, kCommThreads, 0, s, *c, *a);
-  else DDL_LAUNCH(sync_push_update_pull_kernel<2>, grid, kCommThreads, 0, s, *c, *a);
+  static const int cap = getenv("DDL_COMM_CAP") ? atoi(getenv("DDL_COMM_CAP")) : 148;
+  if (a->nbuckets > 1 && a->bucket == 0 && grid > cap) grid = cap;
+  // bandwidth-bound ranges (>= 16 float4 per thread at the chosen grid): 4 float4 per thread per trip; smaller
+  // ranges are latency-bound, and multimem loads measured faster with one (profiles/comm_roofline.md)
+  static const int force_u = getenv("DDL_COMM_UNROLL") ? atoi(getenv("DDL_COMM_UNROLL")) : 0;
+  const bool wide = force_u ? force_u > 1 : (c->mc_grads == nullptr && elems / 4 >= (int64_t)grid * kCommThreads * 16);
+  if (wide) {
+    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 4>), grid, kCommThreads, 0, s, *c, *a);
+    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 4>), grid, kCommThreads, 0, s, *c, *a);
+    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 4>), grid, kCommThreads, 0, s, *c, *a);
+  } else {
+    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 1>), grid, kCommThreads, 0, s, *c, *a);
+    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 1>), grid, kCommThreads, 0, s, *c, *a);
+    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 1>), grid, kCommThreads, 0, s, *c, *a);
+  }
   DDL_LAUNCH_CHECK();
   return 0;
 }

@@ -149,6 +149,11 @@ class FusedTransport(SpmdTransport):
                     raise native.NativeError("GPU %d cannot access GPU %d: no NVLink/P2P path" % (device.index or 0, r))
         nbytes = plan.total * 4
         want_mc = cfg.nvls if cfg.mode == "sync" else "off"
+        if want_mc == "auto" and world < 4:
+            # bytes per rank and direction: peer loads/stores 2(W-1)/W arenas, multimem (1 + 1/W) arenas - the switch
+            # path only moves less for W > 3 (measured at W = 2: 1.03 ms vs 0.67 ms for a 381 MB arena,
+            # profiles/comm_roofline.md)
+            want_mc = "off"
         mem = {"params": _alloc_arena(nbytes, layout.rank, world, device, want_mc),
                "grads": _alloc_arena(nbytes, layout.rank, world, device, want_mc),
                "pad": SymmetricMemory(native.PAD_SLOTS * 4, layout.rank, world, device)}

@@ -161,6 +161,14 @@ def main():
         os.environ["DDL_NVLS"] = "off"
         case_sync(rank, world, "colocated", "greedy", graphs=True, opt="adam", k4=False, nvls="off")
         case_sync_vs_nccl(rank, world, "colocated", "block", "adam", nvls="off")
+    elif case == "sync_nvls_on":
+        try:
+            case_sync(rank, world, "colocated", "greedy", graphs=True, opt="adam", k4=False, nvls="on")
+            case_sync_vs_nccl(rank, world, "colocated", "block", "adam", nvls="on")
+        except Exception as e:                       # noqa: BLE001
+            if "NVLS multicast" not in str(e):
+                raise
+            print("no NVLS on this box: %s" % e, flush=True)
     elif case == "async_sgd":
         case_async_counting(rank, world, "sgd")
     elif case == "async_adam":

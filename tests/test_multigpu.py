@@ -18,6 +18,6 @@ def run_case(case, nproc=2, timeout=300):
     assert r.returncode == 0 and "MGPU_OK " + case in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
-@pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "sync_vs_nccl", "sync_nvls_off", "async_sgd", "async_adam", "async_train"])
+@pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "sync_vs_nccl", "sync_nvls_off", "sync_nvls_on", "async_sgd", "async_adam", "async_train"])
 def test_fused_transport(case):
     run_case(case)
