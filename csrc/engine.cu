@@ -23,6 +23,7 @@ struct FwdPlans {                  // forward plans for one batch size
   DdlTcPlan* conv[3] = {nullptr, nullptr, nullptr};    // conv2..conv4
   DdlTcPlan* fc[2] = {nullptr, nullptr};                // fc1, fc2
   int conv_split[3] = {1, 1, 1};
+  bool fused_pool[3] = {false, false, false};           // conv plan's epilogue is bias + ReLU + pool
   void destroy() {
     for (auto& p : conv) { ddl_tc_plan_destroy(p); p = nullptr; }
     for (auto& p : fc) { ddl_tc_plan_destroy(p); p = nullptr; }
@@ -58,6 +59,7 @@ struct DdlEngine {
   DdlTcPlan* wg_conv[3] = {};
   DdlTcPlan* dg_conv[3] = {};
   int dg_split[3] = {1, 1, 1};
+  bool dg_unpool[3] = {false, false, false};   // dgrad plan's epilogue is the pool + ReLU backward of the layer below
   DdlTcPlan* wg_fc[2] = {};
   DdlTcPlan* dg_fc[2] = {};        // dg_fc[0]: fc1 -> dp4 (cnn only), dg_fc[1]: fc2 -> dh1
   std::vector<void*> allocs;
@@ -71,6 +73,10 @@ struct DdlEngine {
   cudaStream_t side2 = nullptr;    // the overlapped push/update/pull bucket: must not delay the remaining wgrads
   cudaEvent_t ev_fork[8] = {};
   cudaEvent_t ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr;
+  // one stream per conv weight-gradient kernel: they only depend on their own dY, and serialising them on one
+  // stream made that stream the critical path of the backward (tools/timeline.py)
+  cudaStream_t wside[2] = {nullptr, nullptr};       // conv3 / conv2 wgrads (conv4 + FC wgrads stay on `side`)
+  cudaEvent_t ev_wjoin[2] = {nullptr, nullptr}, ev_w0 = nullptr, ev_main2 = nullptr;
 
   const float* P(int v) const { return cfg.params + cfg.var_offset[v]; }
   float* G(int v) const { return cfg.grads + cfg.var_offset[v]; }
@@ -102,6 +108,33 @@ void pick_tiling(int pix_tiles, int nout, int kiters, bool allow_split, int* nti
   *ntile = nt; *ksplit = ks;
 }
 
+// conv plans with a staged (pool / un-pool) epilogue.  Measured (tools/pool_perf.py, profiles/pool_fusion.md): the
+// fastest (N tile, cluster split) is the one whose grid comes closest to ~208 CTAs (two resident per SM on 104 SMs
+// worth of clusters) from below, ties going to the wider cluster, then the wider tile.  Larger batches (no choice
+// fits): widest tile, no split.  DDL_POOL_NT / DDL_POOL_CL override both (perf experiments).
+void pick_staged_tiling(int pix_tiles, int nout, int kiters, int* ntile, int* cluster) {
+  int best_nt = 0, best_cl = 1, best_ctas = -1;
+  for (int nt : {256, 128, 64, 32}) {
+    if (nout % nt) continue;
+    if (best_nt == 0) best_nt = nt;                       // fallback: widest legal tile, unsplit
+    for (int cl : {8, 4, 2, 1}) {
+      if (kiters / cl < 4 || (nt / cl) % 4 || nt / cl < 8) continue;
+      const int ctas = pix_tiles * (nout / nt) * cl;
+      if (ctas > 210) continue;
+      if (ctas > best_ctas) { best_ctas = ctas; best_nt = nt; best_cl = cl; }
+    }
+  }
+  if (best_nt == 0) best_nt = 32;
+  if (getenv("DDL_POOL_NT") && nout % atoi(getenv("DDL_POOL_NT")) == 0) best_nt = atoi(getenv("DDL_POOL_NT"));
+  if (getenv("DDL_POOL_CL")) best_cl = atoi(getenv("DDL_POOL_CL"));
+  *ntile = best_nt; *cluster = best_cl;
+}
+
+bool fuse_pool_enabled() {
+  static const bool on = getenv("DDL_NO_POOL_FUSE") == nullptr;
+  return on;
+}
+
 // FC layers (one pixel tile, M <= 128 rows): the work is streaming the weight matrix once, so spread it
 // over ~a wave of SMs with narrow N tiles and a cluster split over K (the fused epilogue survives).
 void pick_fc_tiling(int nout, int kiters, int* ntile, int* ksplit) {
@@ -131,6 +164,19 @@ int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!probe) return -1;
     int nt, ks;
+    if (fuse_pool_enabled()) {
+      // conv + bias + ReLU + pool in one kernel: no raw buffer, no zeroing, no pool launch
+      ddl_tc_plan_destroy(probe);
+      probe = ddl_tc_plan_conv_pool(e->pooled[l - 1], e->P(v), e->P(v + 1), e->pooled[l], nullptr, B, S, S, cin, cout, 5, 32, 1);
+      if (!probe) return -1;
+      pick_staged_tiling(pix_tiles_of(probe), cout, 25 * cdiv(cin, 32), &nt, &ks);
+      ddl_tc_plan_destroy(probe);
+      out->conv[l - 1] = ddl_tc_plan_conv_pool(e->pooled[l - 1], e->P(v), e->P(v + 1), e->pooled[l], train ? e->idx[l] : nullptr,
+                                               B, S, S, cin, cout, 5, nt, ks);
+      if (!out->conv[l - 1]) return -1;
+      out->fused_pool[l - 1] = true;
+      continue;
+    }
     pick_tiling(pix_tiles_of(probe), cout, 25 * cdiv(cin, 32), true, &nt, &ks);
     ddl_tc_plan_destroy(probe);
     out->conv[l - 1] = ddl_tc_plan_act(0, e->pooled[l - 1], e->P(v), e->raw, B, S, S, cin, cout, 5, nt, ks, 0,
@@ -189,6 +235,17 @@ int build_bwd(DdlEngine* e) {
                                         nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!probe2) return -1;
     int nt, ks;
+    if (fuse_pool_enabled()) {
+      // dgrad + un-pool + ReLU mask + bias gradient of layer l-1 in one kernel: writes dfull[l-1] directly
+      pick_staged_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), &nt, &ks);
+      ddl_tc_plan_destroy(probe2);
+      const int US = e->S[l - 1];
+      e->dg_conv[l - 1] = ddl_tc_plan_dgrad_unpool(e->dfull[l], e->P(v), e->idx[l - 1], e->dfull[l - 1],
+                                                   l - 1 >= 1 ? e->G(v - 1) : nullptr, B, S, S, US, US, cout, cin, 5, nt, ks);
+      if (!e->dg_conv[l - 1]) return -1;
+      e->dg_unpool[l - 1] = true;
+      continue;
+    }
     pick_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), true, &nt, &ks);
     ddl_tc_plan_destroy(probe2);
     e->dg_conv[l - 1] = ddl_tc_plan_act(1, e->dfull[l], e->P(v), e->dpool[l - 1], B, S, S, cout, cin, 5, nt, ks, 0,
@@ -217,6 +274,10 @@ int forward(DdlEngine* e, FwdPlans* fp, const float* x, int B, bool train, cudaS
     v = 2;
     for (int l = 1; l < e->nconv; ++l, v += 2) {
       const int S = e->S[l], cout = e->C[l + 1];
+      if (fp->fused_pool[l - 1]) {
+        if (ddl_tc_plan_run(fp->conv[l - 1], s)) return -1;
+        continue;
+      }
       if (fp->conv_split[l - 1] > 1)
         DDL_CHECK_CUDA(cudaMemsetAsync(e->raw, 0, (size_t)B * S * S * cout * sizeof(float), s));
       if (ddl_tc_plan_run(fp->conv[l - 1], s)) return -1;
@@ -270,6 +331,12 @@ DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg) {
   for (auto& ev : e->ev_fork)
     if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   if (cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
+  for (int i = 0; i < 2; ++i) {
+    if (cudaStreamCreateWithFlags(&e->wside[i], cudaStreamNonBlocking) != cudaSuccess) return fail(e, "wgrad stream");
+    if (cudaEventCreateWithFlags(&e->ev_wjoin[i], cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
+  }
+  if (cudaEventCreateWithFlags(&e->ev_w0, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_main2, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   if (alloc(e, (void**)&e->h1, mb * e->F[1] * 4) || alloc(e, (void**)&e->h2, mb * e->F[2] * 4) ||
       alloc(e, (void**)&e->dh1, (size_t)cfg->batch * e->F[1] * 4) || alloc(e, (void**)&e->dh2, (size_t)cfg->batch * e->F[2] * 4) ||
       alloc(e, (void**)&e->logits, mb * 16 * 4) || alloc(e, (void**)&e->dlogits, (size_t)cfg->batch * 16 * 4) ||
@@ -296,6 +363,12 @@ void ddl_engine_destroy(DdlEngine* e) {
   if (e->ev_join2) cudaEventDestroy(e->ev_join2);
   if (e->side) cudaStreamDestroy(e->side);
   if (e->side2) cudaStreamDestroy(e->side2);
+  for (int i = 0; i < 2; ++i) {
+    if (e->ev_wjoin[i]) cudaEventDestroy(e->ev_wjoin[i]);
+    if (e->wside[i]) cudaStreamDestroy(e->wside[i]);
+  }
+  if (e->ev_w0) cudaEventDestroy(e->ev_w0);
+  if (e->ev_main2) cudaEventDestroy(e->ev_main2);
   delete e;
 }
 
@@ -325,42 +398,75 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   // Main stream: the data-gradient chain.  Side stream: every weight-gradient GEMM, forked as soon as its
   // dY exists and joined once before the optimizer.
   cudaStream_t w = e->side;
+  static const bool one_wstream = getenv("DDL_ONE_WGRAD_STREAM") != nullptr;
+  // stream of layer l's conv wgrad (l = 3, 2, 1 <-> conv4, conv3, conv2)
+  auto wstream = [&](int l) -> cudaStream_t { return (one_wstream || l == 3) ? w : e->wside[2 - l]; };
   int fk = 0;
-  auto fork = [&]() -> int {
+  auto fork = [&](cudaStream_t to) -> int {
     DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork[fk], s));
-    DDL_CHECK_CUDA(cudaStreamWaitEvent(w, e->ev_fork[fk], 0));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(to, e->ev_fork[fk], 0));
     ++fk;
     return 0;
   };
-  if (fork()) return -1;
+  // the overlapped push bucket (conv3..fc3) may start once the wgrads of conv3 (its own stream) and of conv4 / fc1 /
+  // fc2 (stream w) are done; the bias gradients come from main-stream kernels that both already waited for
+  // ... and once conv3's dgrad - the last reader of a weight this bucket updates in place - has run on the main stream
+  auto launch_overlap = [&](cudaStream_t after_conv3) -> int {
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork2, after_conv3));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fork2, 0));
+    if (after_conv3 != w) DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_w0, 0));
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_main2, s));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_main2, 0));
+    for (int i = 0; i < e->ov_n; ++i)
+      if (ddl_sync_push_update_pull(&e->ov_comm, &e->ov_args[i], e->ov_kind, e->side2)) return -1;
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_join2, e->side2));
+    return 0;
+  };
+  if (fork(w)) return -1;
   if (ddl_tc_plan_run(e->wg_fc[1], w)) return -1;
   if (ddl_tc_plan_run(e->dg_fc[1], s)) return -1;      // + fc1 bias gradient in its epilogue
-  if (fork()) return -1;
+  if (fork(w)) return -1;
   if (ddl_tc_plan_run(e->wg_fc[0], w)) return -1;
   if (ddl_tc_plan_needs_zero(e->dg_fc[0]))             // plain split-K output: partial sums are red.add-ed
     DDL_CHECK_CUDA(cudaMemsetAsync(e->dpool[3], 0, (size_t)B * e->F[0] * sizeof(float), s));
   if (ddl_tc_plan_run(e->dg_fc[0], s)) return -1;
   int v = 6;
-  for (int l = 3; l >= 1; --l, v -= 2) {           // conv4, conv3, conv2
+  const bool unpool = e->dg_unpool[0] && e->dg_unpool[1] && e->dg_unpool[2];
+  if (unpool) {
+    // dp4 -> dY of conv4 (the only stand-alone pool backward left); every conv dgrad then writes the dY of the layer
+    // below itself
+    if (ddl_maxpool_bwd(e->dpool[3], e->idx[3], e->dfull[3], e->G(7), B, e->S[3], e->S[3], e->C[4], s)) return -1;
+    for (int l = 3; l >= 1; --l) {
+      cudaStream_t wl = wstream(l);
+      if (fork(wl)) return -1;
+      if (ddl_tc_plan_run(e->wg_conv[l - 1], wl)) return -1;
+      if (l == 3) DDL_CHECK_CUDA(cudaEventRecord(e->ev_w0, w));
+      if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
+      if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
+    }
+  }
+  for (int l = unpool ? 0 : 3; l >= 1; --l, v -= 2) {           // conv4, conv3, conv2
     const int S = e->S[l], cout = e->C[l + 1], cin = e->C[l];
     if (e->dg_split[l - 1] > 1)
       DDL_CHECK_CUDA(cudaMemsetAsync(e->dpool[l - 1], 0, (size_t)B * S * S * cin * sizeof(float), s));
     if (ddl_maxpool_bwd(e->dpool[l], e->idx[l], e->dfull[l], e->G(v + 1), B, S, S, cout, s)) return -1;
-    if (fork()) return -1;
-    if (ddl_tc_plan_run(e->wg_conv[l - 1], w)) return -1;
-    if (l == 2 && e->ov_n > 0) {                   // every gradient of conv3..fc3 is complete once stream w gets here
-      DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork2, w));
-      DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fork2, 0));
-      for (int i = 0; i < e->ov_n; ++i)
-        if (ddl_sync_push_update_pull(&e->ov_comm, &e->ov_args[i], e->ov_kind, e->side2)) return -1;
-      DDL_CHECK_CUDA(cudaEventRecord(e->ev_join2, e->side2));
-    }
+    cudaStream_t wl = wstream(l);
+    if (fork(wl)) return -1;
+    if (ddl_tc_plan_run(e->wg_conv[l - 1], wl)) return -1;
+    if (l == 3) DDL_CHECK_CUDA(cudaEventRecord(e->ev_w0, w));
     if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
+    if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
   }
-  if (ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull[0], nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
+  if (!unpool && ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull[0], nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
   if (ddl_conv1_wgrad(x, e->dfull[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
   DDL_CHECK_CUDA(cudaEventRecord(e->ev_join, w));
   DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join, 0));
+  if (!one_wstream) {
+    for (int i = 0; i < 2; ++i) {
+      DDL_CHECK_CUDA(cudaEventRecord(e->ev_wjoin[i], e->wside[i]));
+      DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_wjoin[i], 0));
+    }
+  }
   if (e->ov_n > 0) DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join2, 0));
   return 0;
 }

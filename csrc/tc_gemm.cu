@@ -63,6 +63,12 @@ struct ActParams {
   uint32_t drop_stream_off;
   uint32_t drop_thresh24;
   float drop_inv_keep;
+  // EPI_POOL / EPI_UNPOOL (staged epilogues, see the kernel)
+  int bars_off;                    // byte offset of PipeBars (past the pipeline stages AND the staging areas)
+  float* pool_out;                 // EPI_POOL: [N, ceil(H/2), ceil(W/2), nout]; EPI_UNPOOL: [N, UH, UW, nout]
+  uint8_t* pool_idx;               // argmax slots: written by EPI_POOL (nullable), read by EPI_UNPOOL
+  int UH, UW;                      // EPI_UNPOOL: un-pooled plane (H = ceil(UH/2), W = ceil(UW/2))
+  float* dbias;                    // EPI_UNPOOL: += column sums of the routed gradient (nullable)
 };
 
 struct WgradParams {
@@ -79,7 +85,8 @@ struct WgradParams {
   float* out;                      // [taps][cb][ca], accumulated with red.add
 };
 
-enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16, EPI_COLSUM = 32 };
+enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16, EPI_COLSUM = 32,
+       EPI_POOL = 64, EPI_UNPOOL = 128 };
 
 struct alignas(8) PipeBars {
   uint64_t full[kMaxStages];
@@ -101,6 +108,10 @@ __device__ __forceinline__ void quad_transpose4(float r[4], int ql) {
   if (b1) { r[0] = rx; r[1] = ry; } else { r[2] = rx; r[3] = ry; }
 }
 
+// Column position inside a staging row of cw floats: channel quads are de-interleaved (c -> (c % 4) * cw/4 + c/4) so
+// that a thread finishing 4 consecutive channels reads 4 conflict-free words (lanes = consecutive quads).
+__device__ __forceinline__ int spos(int c, int cw) { return (c & 3) * (cw >> 2) + (c >> 2); }
+
 __device__ __forceinline__ uint32_t tmem_cols_for(int n) {
   return n <= 32 ? 32u : n <= 64 ? 64u : n <= 128 ? 128u : 256u;
 }
@@ -120,7 +131,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const int a_bytes = kTileM * 128;
   const int b_bytes = p.ntile * 128;
   const int stage_bytes = a_bytes + b_bytes;
-  PipeBars* bars = (PipeBars*)(smem + (size_t)p.stages * stage_bytes);
+  PipeBars* bars = (PipeBars*)(smem + (size_t)p.bars_off);
 
   const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
   const int tile = blockIdx.x;
@@ -133,6 +144,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const int niter = max(0, k_end - k_begin);
   const uint32_t ncols = tmem_cols_for(p.ntile);
   const bool creduce = p.cluster > 1;
+  const bool staged = (p.flags & (EPI_POOL | EPI_UNPOOL)) != 0;
   const uint32_t crank = creduce ? cluster_ctarank() : 0u;
   const int tile_lin = blockIdx.y * gridDim.x + blockIdx.x;
 
@@ -273,6 +285,37 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     }
     if (niter == 0 && elect_one()) umma_commit(&bars->tmem_full);
     __syncwarp();
+  } else if (staged) {
+    // ================= staged epilogue, phase 1 (warps 2..5): accumulator -> shared memory.
+    // The pipeline stages are dead once tmem_full fires (every MMA has read its operands), so they are reused:
+    //   cluster > 1: D[col][row] (column-major, 128 rows) - the partial tile the cluster's CTAs read from each other;
+    //   cluster == 1: straight into S[row][cw + 1] with the bias added.
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    if (lane == 0) mbar_wait(&bars->tmem_full, 0);
+    __syncwarp();
+    tc_fence_after();
+    float* D = reinterpret_cast<float*>(smem);
+    const int sp = p.ntile / p.cluster + 1;
+    for (int c0 = 0; c0 < p.ntile; c0 += 16) {
+      float v[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+      if (niter == 0) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = 0.f;
+      }
+      if (creduce) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) D[(c0 + j) * 128 + row] = v[j];       // a warp writes 128 contiguous bytes
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int col = nt0 + c0 + j;
+          const float b = ((p.flags & EPI_POOL) && col < p.nout) ? __ldg(p.bias + col) : 0.f;
+          D[row * sp + spos(c0 + j, p.ntile)] = v[j] + b;                   // odd pitch: conflict-free
+        }
+      }
+    }
   } else if (creduce && crank != 0) {
     // ================= split-K peer (warps 2..5): park the partial accumulator for the cluster leader
     const int q = warp & 3;
@@ -301,7 +344,151 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     cluster_wait_acquire();
   }
   if (ptrace && threadIdx.x == 64) p.trace[6] = ddl_globaltimer();
-  if (warp >= 2 && (!creduce || crank == 0)) {
+  if (staged) {
+    if (warp >= 2) {
+      // ================= staged epilogue, phases 2 + 3 (warps 2..5, 128 threads)
+      // phase 2 (cluster > 1): reduce-scatter over distributed shared memory - rank r sums columns
+      //   [r * cw, (r + 1) * cw) of all CTAs' D (fixed order: reproducible), + bias, into its own S[row][cw + 1];
+      // phase 3: EPI_POOL   - 2x2 stride-2 SAME max-pool with the running max started at 0 (= ReLU) -> pool_out, pool_idx
+      //          EPI_UNPOOL - route each value to its window's argmax slot of the un-pooled plane, zeros elsewhere
+      //                       (ReLU-dead windows: idx 4 -> all zeros), column sums -> dbias.
+      const int te = (int)threadIdx.x - 64;
+      const int cw = p.ntile / p.cluster, sp = cw + 1;
+      const int colbase = nt0 + (int)crank * cw;
+      float* S = reinterpret_cast<float*>(smem) + (creduce ? (size_t)p.ntile * 128 : 0);
+      if (creduce) {
+        const int rg = te & 31, cq = te >> 5;
+        uint32_t peer[8];
+        const uint32_t d0 = smem_u32(smem);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) peer[k] = cluster_map_shared(d0, (uint32_t)(k < p.cluster ? k : 0));
+        for (int c = cq; c < cw; c += 4) {
+          const uint32_t off = (uint32_t)((((int)crank * cw + c) * 128 + 4 * rg) * 4);
+          float4 t[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (k < p.cluster) t[k] = ld_dsmem_v4(peer[k] + off);
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (k < p.cluster) { acc.x += t[k].x; acc.y += t[k].y; acc.z += t[k].z; acc.w += t[k].w; }
+          const float b = ((p.flags & EPI_POOL) && colbase + c < p.nout) ? __ldg(p.bias + colbase + c) : 0.f;
+          const int cp = spos(c, cw);
+          S[(4 * rg + 0) * sp + cp] = acc.x + b;
+          S[(4 * rg + 1) * sp + cp] = acc.y + b;
+          S[(4 * rg + 2) * sp + cp] = acc.z + b;
+          S[(4 * rg + 3) * sp + cp] = acc.w + b;
+        }
+      }
+      named_bar_sync(1, 128);
+      const int cq4 = cw >> 2;                   // channel quads per staging row; a thread finishes one quad per item
+      float* __restrict__ pout = p.pool_out;
+      if (p.flags & EPI_POOL) {
+        uint8_t* __restrict__ pidx = p.pool_idx;
+        const int PH = (p.H + 1) / 2, PW = (p.W + 1) / 2;
+        const int pbw = (p.bw + 1) / 2, pbh = (p.bh + 1) / 2;
+        const int items = pbw * pbh * p.bn * cq4;
+        for (int it = te; it < items; it += 128) {
+          const int c4 = it % cq4, pp = it / cq4;
+          const int prw = pp % pbw, prh = (pp / pbw) % pbh, prn = pp / (pbw * pbh);
+          const int gpw = w0 / 2 + prw, gph = h0 / 2 + prh, gn = n0 + prn;
+          const int col = colbase + 4 * c4;
+          if (gn >= p.N || gph >= PH || gpw >= PW || col >= p.nout) continue;
+          float best[4] = {0.f, 0.f, 0.f, 0.f};
+          int bi[4] = {4, 4, 4, 4};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int lh = 2 * prh + (k >> 1), lw = 2 * prw + (k & 1);
+            if (lh < p.bh && lw < p.bw && h0 + lh < p.H && w0 + lw < p.W) {
+              const float* sr = S + ((prn * p.bh + lh) * p.bw + lw) * sp + c4;
+#pragma unroll
+              for (int q4 = 0; q4 < 4; ++q4) {
+                const float x = sr[q4 * cq4];
+                if (x > best[q4]) { best[q4] = x; bi[q4] = k; }
+              }
+            }
+          }
+          const int64_t o = (((int64_t)gn * PH + gph) * PW + gpw) * p.nout + col;
+          *reinterpret_cast<float4*>(pout + o) = make_float4(best[0], best[1], best[2], best[3]);
+          if (pidx) *reinterpret_cast<uchar4*>(pidx + o) = make_uchar4(bi[0], bi[1], bi[2], bi[3]);
+        }
+      } else {
+        const uint8_t* __restrict__ pidx = p.pool_idx;
+        const int R = p.bw * p.bh * p.bn;
+        const int items = R * cq4;
+        const bool fixed_col = (128 % cq4) == 0;     // then it % cq4 is the same on every trip of a thread
+        float dbsum[4] = {0.f, 0.f, 0.f, 0.f};
+        // two items per trip, every global load (argmax slots) issued before the first store
+        for (int it0 = te; it0 < items; it0 += 256) {
+          uchar4 bi[2];
+          float g[2][4];
+          int64_t obase[2];
+          int gh[2], gw[2], colv[2];
+          bool ok[2];
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int it = it0 + u * 128;
+            const int c4 = it % cq4, r = it / cq4;
+            const int rw = r % p.bw, rh = (r / p.bw) % p.bh, rn = r / (p.bw * p.bh);
+            const int gn = n0 + rn;
+            gw[u] = w0 + rw; gh[u] = h0 + rh;
+            colv[u] = colbase + 4 * c4;
+            ok[u] = it < items && gn < p.N && gh[u] < p.H && gw[u] < p.W && colv[u] < p.nout;
+            bi[u] = make_uchar4(4, 4, 4, 4);
+            if (ok[u]) {
+              bi[u] = *reinterpret_cast<const uchar4*>(pidx + (((int64_t)gn * p.H + gh[u]) * p.W + gw[u]) * p.nout + colv[u]);
+              const float* sr = S + r * sp + c4;
+#pragma unroll
+              for (int q4 = 0; q4 < 4; ++q4) g[u][q4] = sr[q4 * cq4];
+            }
+            obase[u] = (int64_t)gn * p.UH;
+          }
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            if (!ok[u]) continue;
+            const int b4[4] = {bi[u].x, bi[u].y, bi[u].z, bi[u].w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int uh = 2 * gh[u] + (k >> 1), uw = 2 * gw[u] + (k & 1);
+              if (uh < p.UH && uw < p.UW)
+                *reinterpret_cast<float4*>(pout + ((obase[u] + uh) * p.UW + uw) * p.nout + colv[u]) =
+                    make_float4(b4[0] == k ? g[u][0] : 0.f, b4[1] == k ? g[u][1] : 0.f, b4[2] == k ? g[u][2] : 0.f,
+                                b4[3] == k ? g[u][3] : 0.f);
+            }
+            if (p.dbias) {
+#pragma unroll
+              for (int q4 = 0; q4 < 4; ++q4) {
+                if (b4[q4] < 4) {
+                  if (fixed_col) dbsum[q4] += g[u][q4];
+                  else if (g[u][q4] != 0.f) atomicAdd(p.dbias + colv[u] + q4, g[u][q4]);
+                }
+              }
+            }
+          }
+        }
+        if (p.dbias && fixed_col) {
+          // lanes cq4 apart hold the same channel quad: fold them with shuffles, one atomic per warp and channel
+          const bool pow2 = (cq4 & (cq4 - 1)) == 0;
+          if (pow2) {
+            for (int off = cq4; off < 32; off <<= 1) {
+#pragma unroll
+              for (int q4 = 0; q4 < 4; ++q4) dbsum[q4] += __shfl_xor_sync(0xffffffffu, dbsum[q4], off);
+            }
+          }
+          const int col = colbase + 4 * (te % cq4);
+          if (!pow2 || cq4 >= 32 || lane < cq4) {
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4)
+              if (dbsum[q4] != 0.f && col + q4 < p.nout) atomicAdd(p.dbias + col + q4, dbsum[q4]);
+          }
+        }
+      }
+    }
+    if (creduce) {                           // nobody leaves (or frees its shared memory) while a peer may still read D
+      cluster_arrive_release();
+      cluster_wait_acquire();
+    }
+  } else if (warp >= 2 && (!creduce || crank == 0)) {
     // ================= epilogue (warps 2..5) =================
     const int q = warp & 3;                      // TMEM lane quarter this warp may read
     const int row = q * 32 + lane;
@@ -603,19 +790,23 @@ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // the number of tiles (ties: fewer rows).  bh / bn may overshoot the tensor by up to row_mult-1:
 // TMA zero-fills out-of-bounds rows, which contribute nothing to a reduction and are skipped by
 // the epilogue of the act kernel.
-void choose_box(int N, int H, int W, int max_rows, int row_mult, int* bw, int* bh, int* bn) {
+// even_windows: 2x2 pooling windows never straddle two tiles (tile origins even, extents even or the whole axis).
+void choose_box(int N, int H, int W, int max_rows, int row_mult, int* bw, int* bh, int* bn, bool even_windows = false) {
   int best_tiles = 1 << 30, best_rows = 0;
   *bw = 1; *bh = 1; *bn = row_mult;
   const int hmax = (H + row_mult - 1) / row_mult * row_mult;
   const int nmax = (N + row_mult - 1) / row_mult * row_mult;
   for (int w = 1; w <= W && w <= 256; ++w) {
     if (w != W && W % w != 0) continue;                 // full rows or exact divisors of the width
+    if (even_windows && w != W && (w & 1)) continue;
     for (int h = 1; h <= hmax && h <= 256 && w * h <= max_rows; ++h) {
+      if (even_windows && h < H && (h & 1)) continue;
       for (int n = 1; n <= nmax && n <= 256 && w * h * n <= max_rows; ++n) {
         int rows = w * h * n;
         if (rows % row_mult) continue;
         int tiles = ceil_div(W, w) * ceil_div(H, h) * ceil_div(N, n);
-        if (tiles < best_tiles || (tiles == best_tiles && rows < best_rows)) {
+        if (tiles < best_tiles || (tiles == best_tiles && rows < best_rows) ||
+            (even_windows && tiles == best_tiles && rows == best_rows && w > *bw)) {   // ties: longest contiguous run
           best_tiles = tiles; best_rows = rows; *bw = w; *bh = h; *bn = n;
         }
       }
@@ -636,13 +827,28 @@ struct DdlTcPlan {
   size_t smem;
 };
 
-extern "C" {
+// staged-epilogue options of an act plan (EPI_POOL for fprop, EPI_UNPOOL for dgrad)
+struct PoolOpt {
+  float* out2;            // pooled output / un-pooled gradient
+  uint8_t* idx;           // argmax slots (written / read)
+  float* dbias;           // EPI_UNPOOL: bias gradient (nullable)
+  int UH, UW;             // EPI_UNPOOL: un-pooled plane
+};
 
-DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
-                           int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
-                           const float* mask_act, float mask_scale, const DdlStepState* st,
-                           uint32_t drop_stream_off, float keep_prob, float* colsum, float* w_store_dst) {
+static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
+                                int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
+                                const float* mask_act, float mask_scale, const DdlStepState* st,
+                                uint32_t drop_stream_off, float keep_prob, float* colsum, float* w_store_dst,
+                                const PoolOpt* po) {
   auto fail = [](const char* why) -> DdlTcPlan* { ddl::set_error("ddl_tc_plan_act: %s", why); return nullptr; };
+  if (po) {
+    if (flags || colsum || w_store_dst) return fail("staged pool epilogues take no other epilogue flags");
+    if (ksplit != 1 && ksplit != 2 && ksplit != 4 && ksplit != 8) return fail("staged epilogue: cluster split must be 1, 2, 4 or 8");
+    if (ntile % ksplit || (ntile / ksplit) % 4) return fail("staged epilogue: ntile / split must be a multiple of 4");
+    if (!dgrad && bias == nullptr) return fail("pool epilogue needs the bias");
+    if (dgrad && po->idx == nullptr) return fail("un-pool epilogue needs the argmax slots");
+    flags = dgrad ? EPI_UNPOOL : EPI_POOL;
+  }
   if (cred % 4 || nout % 4) return fail("channel counts must be multiples of 4 (16-byte TMA pitch)");
   if (ntile < 16 || ntile > 256 || ntile % 16) return fail("ntile must be a multiple of 16 in [16, 256]");
   if (!dgrad && ntile % 32) return fail("fprop ntile must be a multiple of 32 (MN-major boxes)");
@@ -652,7 +858,7 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
   pl->kind = 0;
   ActParams& p = pl->act;
   p.N = N; p.H = H; p.W = W;
-  choose_box(N, H, W, kTileM, 1, &p.bw, &p.bh, &p.bn);
+  choose_box(N, H, W, kTileM, 1, &p.bw, &p.bh, &p.bn, po && !dgrad);
   p.tiles_w = ceil_div(W, p.bw); p.tiles_h = ceil_div(H, p.bh); p.tiles_n = ceil_div(N, p.bn);
   p.ksize = ksize; p.flip = dgrad ? 1 : 0;
   p.cblocks = ceil_div(cred, kKB);
@@ -669,12 +875,17 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
   //    fusion and needs no zeroing, but rank 0 alone reads (ksplit-1) tiles: 44.5 us for the same conv4
   //    case, so it is only used where the tile is narrow (N tile 32) and the epilogue must stay fused.
   const bool fused_epi = (flags & (EPI_BIAS | EPI_RELU | EPI_DROPOUT | EPI_MASKPOS)) != 0 || colsum != nullptr;
-  const bool want_cluster = getenv("DDL_TC_NO_CLUSTER") == nullptr &&
-                            (fused_epi || getenv("DDL_TC_FORCE_CLUSTER") != nullptr);
+  const bool want_cluster = po != nullptr || (getenv("DDL_TC_NO_CLUSTER") == nullptr &&
+                                             (fused_epi || getenv("DDL_TC_FORCE_CLUSTER") != nullptr));
+  if (po && p.ksplit != (ksplit < 1 ? 1 : ksplit)) return (delete pl, fail("staged epilogue: split exceeds the k iterations"));
   if (want_cluster && p.ksplit > 8) p.ksplit = 8;
   p.cluster = (want_cluster && p.ksplit > 1) ? p.ksplit : 1;
   p.scratch = nullptr;
   p.flags = flags | ((p.ksplit > 1 && p.cluster == 1) ? EPI_ATOMIC : 0);
+  p.pool_out = po ? po->out2 : nullptr;
+  p.pool_idx = po ? po->idx : nullptr;
+  p.dbias = po ? po->dbias : nullptr;
+  p.UH = po ? po->UH : 0; p.UW = po ? po->UW : 0;
   p.pull = (w_store_dst != nullptr && !dgrad && w_store_dst != w) ? 1 : 0;
   p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
   p.trace = nullptr;
@@ -697,10 +908,22 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages > p.kiters) stages = p.kiters < 2 ? 2 : p.kiters;
   if (getenv("DDL_TC_STAGES")) stages = atoi(getenv("DDL_TC_STAGES"));
+  // staged epilogues reuse the stage memory: D (cluster > 1: ntile x 128 floats) + S (128 x (cw + 1) floats)
+  size_t epi_bytes = 0;
+  if (po) {
+    const int cw = ntile / p.cluster;
+    epi_bytes = (p.cluster > 1 ? (size_t)ntile * 512 : 0) + (size_t)128 * (cw + 1) * sizeof(float);
+    const int per_cta = ceil_div(p.kiters, p.ksplit);
+    while ((size_t)stages * stage_bytes + stage_bytes <= epi_bytes && stages < kMaxStages && stages < per_cta) ++stages;
+  }
   p.stages = stages;
-  pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
+  size_t bars_off = (size_t)stages * stage_bytes;
+  if (epi_bytes > bars_off) bars_off = (epi_bytes + 15) & ~(size_t)15;
+  p.bars_off = (int)bars_off;
+  pl->smem = bars_off + sizeof(PipeBars) + 1024;
+  if (pl->smem > 227 * 1024) return (delete pl, fail("tile does not fit shared memory"));
   pl->grid = dim3(p.tiles_w * p.tiles_h * p.tiles_n, ceil_div(nout, ntile), p.ksplit);
-  if (p.cluster > 1) {
+  if (p.cluster > 1 && !po) {
     const size_t bytes = (size_t)pl->grid.x * pl->grid.y * (p.cluster - 1) * kTileM * ntile * sizeof(float);
     if (cudaMalloc((void**)&pl->scratch, bytes) != cudaSuccess) { delete pl; return fail("cudaMalloc(split-K scratch) failed"); }
     p.scratch = pl->scratch;
@@ -726,6 +949,37 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
     return fail("cudaFuncSetAttribute(max dynamic smem) failed");
   }
   return pl;
+}
+
+extern "C" {
+
+DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* out, int N, int H, int W,
+                           int cred, int nout, int ksize, int ntile, int ksplit, int flags, const float* bias,
+                           const float* mask_act, float mask_scale, const DdlStepState* st,
+                           uint32_t drop_stream_off, float keep_prob, float* colsum, float* w_store_dst) {
+  return plan_act_impl(dgrad, act, w, out, N, H, W, cred, nout, ksize, ntile, ksplit, flags, bias, mask_act, mask_scale,
+                       st, drop_stream_off, keep_prob, colsum, w_store_dst, nullptr);
+}
+
+/* conv fprop whose epilogue is bias + ReLU + 2x2 SAME max-pool: writes pooled [N, ceil(H/2), ceil(W/2), nout] and
+ * (idx != NULL) the argmax slot of every window (0..3, 4 = ReLU-dead).  cluster in {1, 2, 4, 8}: the K loop is split
+ * over a thread-block cluster whose CTAs reduce-scatter their partial tiles through distributed shared memory. */
+DdlTcPlan* ddl_tc_plan_conv_pool(const float* act, const float* w, const float* bias, float* pooled, uint8_t* idx,
+                                 int N, int H, int W, int cin, int cout, int ksize, int ntile, int cluster) {
+  PoolOpt po = {pooled, idx, nullptr, 0, 0};
+  return plan_act_impl(0, act, w, nullptr, N, H, W, cin, cout, ksize, ntile, cluster, 0, bias, nullptr, 1.f, nullptr, 0,
+                       1.f, nullptr, nullptr, &po);
+}
+
+/* conv dgrad whose epilogue is the pool + ReLU backward of the layer below: dY [N, H, W, cout] -> gradient of the
+ * un-pooled plane [N, UH, UW, cin] (value at the window's argmax slot, zeros elsewhere) and dbias += its column sums. */
+DdlTcPlan* ddl_tc_plan_dgrad_unpool(const float* dy, const float* w, const uint8_t* idx, float* dfull, float* dbias,
+                                    int N, int H, int W, int UH, int UW, int cout, int cin, int ksize, int ntile,
+                                    int cluster) {
+  PoolOpt po = {dfull, const_cast<uint8_t*>(idx), dbias, UH, UW};
+  if ((UH + 1) / 2 != H || (UW + 1) / 2 != W) { ddl::set_error("ddl_tc_plan_dgrad_unpool: plane %dx%d does not pool to %dx%d", UH, UW, H, W); return nullptr; }
+  return plan_act_impl(1, dy, w, nullptr, N, H, W, cout, cin, ksize, ntile, cluster, 0, nullptr, nullptr, 1.f, nullptr, 0,
+                       1.f, nullptr, nullptr, &po);
 }
 
 DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,

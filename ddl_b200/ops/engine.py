@@ -8,6 +8,8 @@ CUDA graph.
 """
 from __future__ import annotations
 
+import os
+
 import ctypes as C
 from typing import Optional, Tuple
 
@@ -69,7 +71,9 @@ class NativeBackend:
         advanced (``advance_state``) by the caller."""
         native.check(self.L.ddl_engine_train_step(self.h, native.ptr(x), native.ptr(y), native.stream_ptr()),
                      "ddl_engine_train_step")
-        native.count(26 + getattr(self, "overlap_launches", 0))    # 26 engine kernels (+ the overlapped push bucket)
+        # engine kernels per step: 20 with the pools fused into the conv / dgrad epilogues, 26 with DDL_NO_POOL_FUSE
+        # (+ the overlapped push bucket)
+        native.count((26 if os.environ.get("DDL_NO_POOL_FUSE") else 20) + getattr(self, "overlap_launches", 0))
 
     def advance_state(self, advance_opt: bool = True) -> None:
         c = self.cfg
@@ -103,7 +107,7 @@ class NativeBackend:
             native.check(self.L.ddl_engine_eval(self.h, x[b:e].data_ptr(), y[b:e].data_ptr(), e - b,
                                                 self._correct.data_ptr(), None, native.stream_ptr()),
                          "ddl_engine_eval")
-            native.count(11)
+            native.count(11 if os.environ.get("DDL_NO_POOL_FUSE") else 8)
         return int(self._correct.item()), n
 
     @torch.no_grad()

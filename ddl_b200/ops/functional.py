@@ -59,6 +59,34 @@ def conv5x5_dgrad(dy: torch.Tensor, w: torch.Tensor, ntile: int = 0, ksplit: int
     return out
 
 
+def conv5x5_relu_pool(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, ntile: int = 0, cluster: int = 1,
+                      want_idx: bool = True):
+    """conv + bias + ReLU + 2x2 SAME max-pool in ONE tcgen05 kernel (model.py:39-42); returns (pooled, idx)."""
+    N, H, W, Cin = x.shape
+    k, Cout = w.shape[0], w.shape[3]
+    nt = ntile or min(128, Cout)
+    y = torch.empty(N, (H + 1) // 2, (W + 1) // 2, Cout, device=x.device, dtype=torch.float32)
+    idx = torch.empty(y.shape, device=x.device, dtype=torch.uint8) if want_idx else None
+    plan = native.lib().ddl_tc_plan_conv_pool(native.ptr(x), native.ptr(w), native.ptr(bias), native.ptr(y),
+                                              native.ptr(idx), N, H, W, Cin, Cout, k, nt, cluster)
+    _run_plan(plan)
+    return y, idx
+
+
+def conv5x5_dgrad_unpool(dy: torch.Tensor, w: torch.Tensor, idx: torch.Tensor, UH: int, UW: int, ntile: int = 0,
+                         cluster: int = 1, want_db: bool = True):
+    """conv dgrad + pool/ReLU backward of the layer below in ONE kernel; returns (dfull [N,UH,UW,Cin], dbias)."""
+    N, H, W, Cout = dy.shape
+    k, Cin = w.shape[0], w.shape[2]
+    nt = ntile or min(128, Cin)
+    out = torch.empty(N, UH, UW, Cin, device=dy.device, dtype=torch.float32)
+    db = torch.zeros(Cin, device=dy.device, dtype=torch.float32) if want_db else None
+    plan = native.lib().ddl_tc_plan_dgrad_unpool(native.ptr(dy), native.ptr(w), native.ptr(idx), native.ptr(out),
+                                                 native.ptr(db), N, H, W, UH, UW, Cout, Cin, k, nt, cluster)
+    _run_plan(plan)
+    return out, db
+
+
 def conv5x5_wgrad(dy: torch.Tensor, x: torch.Tensor, ksize: int = 5, ntile: int = 0, psplit: int = 1,
                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """conv2d backprop-filter: dy [N,H,W,Cout], x [N,H,W,Cin] -> dw [k,k,Cin,Cout] (accumulated into out)."""

@@ -108,6 +108,8 @@ def lib() -> C.CDLL:
         "ddl_accuracy": ([vp, vp, vp, i32, i32, vp], i32),
         "ddl_tc_plan_act": ([i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, f32, vp, u32, f32, vp, vp], vp),
         "ddl_tc_plan_wgrad": ([vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
+        "ddl_tc_plan_conv_pool": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
+        "ddl_tc_plan_dgrad_unpool": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_tc_plan_run": ([vp, vp], i32),
         "ddl_tc_plan_destroy": ([vp], None),
         "ddl_tc_plan_info": ([vp, C.POINTER(C.c_int)], i32),

@@ -103,6 +103,19 @@ DdlTcPlan* ddl_tc_plan_act(int dgrad, const float* act, const float* w, float* o
                            uint32_t drop_stream_off, float keep_prob, float* colsum, float* w_store_dst);
 DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,
                              int ksize, int ntile, int psplit);
+/* Convolutions with the layer's pooling fused into the GEMM epilogue (model.py:39-42 / 50-53 / 61-64 in one kernel
+ * forward; the pool + ReLU backward of the layer below in the dgrad kernel).  cluster in {1, 2, 4, 8}: the K loop is
+ * split over a thread-block cluster; its CTAs reduce-scatter their partial accumulator tiles through distributed
+ * shared memory (rank r sums and finishes columns [r * ntile / cluster, (r + 1) * ntile / cluster)), so a split
+ * reduction keeps its fused epilogue and needs neither zeroed outputs nor atomics.
+ *   conv_pool:    pooled[N, ceil(H/2), ceil(W/2), cout] = maxpool2x2_SAME(relu(conv5x5_SAME(act, w) + bias));
+ *                 idx (may be NULL): argmax slot of every window, 0..3, 4 = the window's maximum is <= 0 (no gradient)
+ *   dgrad_unpool: dfull[N, UH, UW, cin] = un-pool(idx, conv dgrad(dy, w)), dbias (may be NULL) += column sums */
+DdlTcPlan* ddl_tc_plan_conv_pool(const float* act, const float* w, const float* bias, float* pooled, uint8_t* idx,
+                                 int N, int H, int W, int cin, int cout, int ksize, int ntile, int cluster);
+DdlTcPlan* ddl_tc_plan_dgrad_unpool(const float* dy, const float* w, const uint8_t* idx, float* dfull, float* dbias,
+                                    int N, int H, int W, int UH, int UW, int cout, int cin, int ksize, int ntile,
+                                    int cluster);
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);
 void ddl_tc_plan_destroy(DdlTcPlan* pl);
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8);

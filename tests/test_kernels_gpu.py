@@ -110,6 +110,64 @@ def test_tc_conv_fprop(H, Cin, Cout, B):
     assert rel_err(outs, ref) < TF32_TOL
 
 
+@pytest.mark.parametrize("H,Cin,Cout,B,ntile,cluster", [
+    (14, 32, 64, 100, 64, 1), (14, 32, 64, 37, 32, 1), (7, 64, 128, 100, 128, 1), (7, 64, 128, 100, 128, 2),
+    (7, 64, 128, 100, 128, 4), (4, 128, 256, 100, 128, 8), (4, 128, 256, 100, 256, 8), (4, 128, 256, 100, 128, 4),
+    (4, 128, 256, 513, 256, 1)])
+def test_tc_conv_relu_pool_fused(H, Cin, Cout, B, ntile, cluster):
+    """conv + bias + ReLU + pool in one kernel (cluster split-K reduced through distributed shared memory)."""
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(11)
+    x = torch.randn(B, H, H, Cin, device=dev())
+    w = torch.randn(5, 5, Cin, Cout, device=dev()) * 0.05
+    bias = torch.randn(Cout, device=dev()) * 0.5
+    act = F.relu(ref_conv(x, w) + bias)                                    # [B,H,H,Cout] fp32 reference
+    ref = F.max_pool2d(act.permute(0, 3, 1, 2), 2, 2, ceil_mode=True).permute(0, 2, 3, 1)
+    y, idx = K.conv5x5_relu_pool(x, w, bias, ntile=ntile, cluster=cluster)
+    assert y.shape == ref.shape
+    assert rel_err(y, ref) < TF32_TOL
+    # the recorded slot points at the window's maximum; slot 4 <=> the pooled value is 0
+    PH = (H + 1) // 2
+    pad = torch.zeros(B, 2 * PH, 2 * PH, Cout, device=dev())
+    pad[:, :H, :H] = act
+    win = pad.view(B, PH, 2, PH, 2, Cout).permute(0, 1, 3, 5, 2, 4).reshape(B, PH, PH, Cout, 4)
+    dead = idx == 4
+    assert torch.equal(dead, y == 0)
+    picked = torch.gather(win, 4, idx.clamp(max=3).long().unsqueeze(-1)).squeeze(-1)
+    assert torch.allclose(torch.where(dead, torch.zeros_like(picked), picked), y, atol=5e-2)
+    # without the slots (evaluation)
+    y2, none = K.conv5x5_relu_pool(x, w, bias, ntile=ntile, cluster=cluster, want_idx=False)
+    assert none is None and rel_err(y2, ref) < TF32_TOL
+
+
+@pytest.mark.parametrize("H,UH,Cin,Cout,B,ntile,cluster", [
+    (14, 28, 32, 64, 100, 32, 1), (7, 14, 64, 128, 100, 64, 1), (7, 14, 64, 128, 100, 64, 4), (7, 14, 64, 128, 100, 32, 2),
+    (4, 7, 128, 256, 100, 128, 8), (4, 7, 128, 256, 100, 64, 8), (4, 7, 128, 256, 37, 128, 2)])
+def test_tc_conv_dgrad_unpool_fused(H, UH, Cin, Cout, B, ntile, cluster):
+    """conv dgrad + pool/ReLU backward of the layer below in one kernel, against the two separate kernels and torch."""
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(12)
+    dy = torch.randn(B, H, H, Cout, device=dev())
+    w = torch.randn(5, 5, Cin, Cout, device=dev()) * 0.05
+    below = torch.randn(B, UH, UH, Cin, device=dev())                      # pre-activation of the layer below
+    _, idx = K.bias_relu_maxpool(below)
+    dp = K.conv5x5_dgrad(dy, w)                                            # [B,H,H,Cin]
+    want, want_db = K.maxpool_relu_bwd(dp, idx, UH, UH)
+    got, db = K.conv5x5_dgrad_unpool(dy, w, idx, UH, UH, ntile=ntile, cluster=cluster)
+    assert got.shape == want.shape
+    assert rel_err(got, want) < 1e-4
+    assert rel_err(db, want_db) < 1e-3
+    assert torch.equal(got == 0, want == 0)
+    # against torch autograd in fp64
+    xb = below.double().requires_grad_(True)
+    p = F.max_pool2d(F.relu(xb).permute(0, 3, 1, 2), 2, 2, ceil_mode=True)
+    y = F.conv2d(p, w.double().permute(3, 2, 0, 1), padding=2).permute(0, 2, 3, 1)
+    y.backward(dy.double())
+    assert rel_err(got, xb.grad.float()) < TF32_TOL
+    got2, none = K.conv5x5_dgrad_unpool(dy, w, idx, UH, UH, ntile=ntile, cluster=cluster, want_db=False)
+    assert none is None and torch.equal(got2, got)
+
+
 @pytest.mark.parametrize("H,Cin,Cout", [(14, 32, 64), (7, 64, 128), (4, 128, 256)])
 def test_tc_conv_dgrad_wgrad(H, Cin, Cout):
     from ddl_b200.ops import functional as K

@@ -19,7 +19,7 @@ def run(label, dgrad, N, H, cred, nout, ks, ntile, ksplit, flags):
     plan = L.ddl_tc_plan_act(dgrad, x.data_ptr(), w.data_ptr(), out.data_ptr(), N, H, H, cred, nout, ks, ntile, ksplit, flags,
                              bias.data_ptr(), None, 1.0, None, 0, 1.0, None, None)
     assert plan, native.last_error()
-    for cold in (True,):
+    for cold in (True, False):
         for _ in range(2):
             if cold:
                 flush.fill_(1)
