@@ -298,6 +298,9 @@ DDL_DEVICE float4 ld_dsmem_v4(uint32_t cluster_addr) {
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(cluster_addr) : "memory");
   return v;
 }
+DDL_DEVICE void st_dsmem_f32(uint32_t cluster_addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(cluster_addr), "f"(v) : "memory");
+}
 // named barrier over `nthreads` threads (id 1..15; 0 is __syncthreads)
 DDL_DEVICE void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
 

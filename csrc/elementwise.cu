@@ -433,65 +433,138 @@ __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restr
   }
 }
 
-// fc3 forward + softmax cross-entropy + fc3 backward in ONE kernel (training path).
-// Every block recomputes the [B, NC] logits (B*K*NC MACs - tiny) so no grid-wide hand-off is needed
-// between "dlogits ready" and the weight / input gradients; block b then owns the 32 k-columns
-// [32b, 32b+32) exactly like fc3_bwd_kernel.  Block 0 alone accumulates the loss / accuracy.
-__global__ void __launch_bounds__(256) fc3_fused_kernel(const float* __restrict__ h, const float* __restrict__ w,
-                                                        const float* __restrict__ bias, const int* __restrict__ labels,
-                                                        float* __restrict__ dw, float* __restrict__ db,
-                                                        float* __restrict__ dh, float* __restrict__ dbh,
-                                                        DdlStepState* st, int B, int K, int NC, float scale,
-                                                        uint32_t stream_off, uint32_t thresh24, float inv_keep) {
-  pdl_enter();
-  extern __shared__ float sm[];
-  __shared__ float colred[8][32];
-  float* sw3 = sm;                        // [K][NC]
-  float* sdl = sw3 + K * NC;              // [B][NC]
-  float* sh = sdl + B * NC;               // [B][32]
-  const int k0 = blockIdx.x * 32;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const uint32_t seed = st->seed, stream = st->stream + stream_off;
-  for (int i = threadIdx.x; i < K * NC; i += blockDim.x) sw3[i] = w[i];
-  for (int i = threadIdx.x; i < B * 32; i += blockDim.x) {
-    const int r = i >> 5, k = k0 + (i & 31);
-    sh[i] = (k < K) ? h[(int64_t)r * K + k] : 0.f;
-  }
-  __syncthreads();
-  // ---- phase 1: logits, softmax, dlogits for every row (warp per row)
-  float loss_acc = 0.f;
-  unsigned correct_acc = 0;
-  for (int row = warp; row < B; row += nwarps) {
-    float acc[16];
+// fc3 forward + softmax cross-entropy + fc3 backward in ONE kernel (training path): a thread-block cluster of
+// kFc3Cluster CTAs x 1024 threads.  CTA r computes the logits / softmax / dlogits of rows r, r + CS, ... (warp per
+// row) and stores each dlogits value into EVERY CTA's shared memory (st.shared::cluster); after one cluster barrier
+// CTA r owns the k-columns [r * KS, (r + 1) * KS) of the backward: dW3, dh2 (+ dropout mask) and the column sums of
+// dh2 (= fc2's bias gradient).  What shaped it (tools/fc3_phase.py, tools/timeline.py): the two-kernel version took
+// 16 + 15 us for ~3 MFLOP because 256-thread blocks walked long dependent LDS -> FMA chains with runtime div / mod
+// per output.  Here: the class count is a compile-time padded width (NCT = 12 or 16, zero columns), every inner loop
+// is vector LDS + independent FMAs, 32 warps per SM hide the latencies, everything that does not depend on the
+// previous kernel (W3 -> shared memory, bias, labels) is loaded BEFORE griddepcontrol.wait.
+constexpr int kFc3Cluster = 8;
+constexpr int kFc3Threads = 1024;
+// perf experiments: globaltimer stamps of CTA 0 / thread 0 (tools/fc3_phase.py); off unless ddl_debug_stamps(1)
+__device__ int g_stamps_on = 0;
+__device__ unsigned long long g_stamps[32];
+#define DDL_STAMP(i) do { if (stamps && threadIdx.x == 0) g_stamps[i] = ddl_globaltimer(); } while (0)
+
+template <int NCT>
+__global__ void __launch_bounds__(kFc3Threads) fc3_cluster_kernel(const float* __restrict__ h, const float* __restrict__ w,
+                                                                  const float* __restrict__ bias, const int* __restrict__ labels,
+                                                                  float* __restrict__ dw, float* __restrict__ db,
+                                                                  float* __restrict__ dh, float* __restrict__ dbh,
+                                                                  DdlStepState* st, int B, int K, int NC, int KS, float scale,
+                                                                  uint32_t stream_off, uint32_t thresh24, float inv_keep) {
+  pdl_launch_dependents();
+  cluster_arrive_release();                // "I am running": peers may store into my shared memory after the matching wait
+  extern __shared__ __align__(16) float sm[];
+  float* swT = sm;                         // [NCT][K]    W3 transposed (rows >= NC are zero): lanes along k, LDS.128
+  float* sdl = swT + NCT * K;              // [B][NCT]    dlogits of every row (filled by all CTAs of the cluster)
+  float* shs = sdl + B * NCT;              // [B][KS + 1] this CTA's k-columns of h
+  float* scol = shs + B * (KS + 1);        // [KS]        column sums of dh
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int crank = (int)cluster_ctarank();
+  const bool stamps = g_stamps_on && crank == 0;
+  DDL_STAMP(0);
+  const int k0 = crank * KS;
+  // ---- phase 0: loads that do not depend on the previous kernel
+  {
+    const int n4 = (K * NC) >> 2;
+    for (int base = 0; base < n4; base += kFc3Threads * 2) {
+      float4 buf[2];
 #pragma unroll
-    for (int c = 0; c < 16; ++c) acc[c] = 0.f;
-    for (int kb = 0; kb < K; kb += 32 * 8) {
-      float hv[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int k = kb + u * 32 + lane;
-        hv[u] = k < K ? h[(int64_t)row * K + k] : 0.f;
+      for (int u = 0; u < 2; ++u) {
+        const int i4 = base + u * kFc3Threads + t;
+        if (i4 < n4) buf[u] = __ldg(reinterpret_cast<const float4*>(w) + i4);
       }
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int k = kb + u * 32 + lane;
-        if (k < K) {
-          const float* wr = sw3 + k * NC;
+      for (int u = 0; u < 2; ++u) {
+        const int i4 = base + u * kFc3Threads + t;
+        if (i4 < n4) {
+          const float v4[4] = {buf[u].x, buf[u].y, buf[u].z, buf[u].w};
+          int kk = (4 * i4) / NC, cc = (4 * i4) % NC;
 #pragma unroll
-          for (int c = 0; c < 16; ++c)
-            if (c < NC) acc[c] += hv[u] * wr[c];
+          for (int j = 0; j < 4; ++j) {
+            swT[cc * K + kk] = v4[j];
+            if (++cc == NC) { cc = 0; ++kk; }
+          }
+        }
+      }
+    }
+    for (int i = t; i < (NCT - NC) * K; i += kFc3Threads) swT[NC * K + i] = 0.f;
+    for (int i = t; i < KS; i += kFc3Threads) scol[i] = 0.f;
+  }
+  const float bz = lane < NC ? __ldg(bias + lane) : 0.f;
+  const int my_row = crank + kFc3Cluster * warp;        // one row per warp: B <= 32 * kFc3Cluster
+  const int lab = my_row < B ? __ldg(labels + my_row) : 0;
+  DDL_STAMP(1);
+  pdl_wait();                                // h (and the step state) come from the previous kernels
+  DDL_STAMP(2);
+  const uint32_t seed = st->seed, stream = st->stream + stream_off;
+  // this CTA's k-columns of h for the backward: issued now, parked in shared memory after the logits
+  constexpr int kHs = 2;
+  float4 hs[kHs];
+  const int ks4 = KS >> 2, nslice4 = B * ks4;
+#pragma unroll
+  for (int u = 0; u < kHs; ++u) {
+    const int o4 = u * kFc3Threads + t;
+    hs[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (o4 < nslice4) {
+      const int r = o4 / ks4, k = k0 + 4 * (o4 % ks4);
+      if (k < K) hs[u] = *reinterpret_cast<const float4*>(h + (int64_t)r * K + k);
+    }
+  }
+  // my row of h: lanes own 4 consecutive k per 128-column chunk
+  float4 hv[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const int k = 4 * lane + 128 * u;
+    hv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (my_row < B && k < K) hv[u] = *reinterpret_cast<const float4*>(h + (int64_t)my_row * K + k);
+  }
+  __syncthreads();                           // swT complete
+  DDL_STAMP(3);
+  cluster_wait_acquire();                    // every CTA of the cluster has started
+  DDL_STAMP(4);
+  // ---- phase 1: logits, softmax, dlogits of my row, pushed into every CTA's sdl
+  if (my_row < B) {
+    float acc[NCT];
+#pragma unroll
+    for (int c = 0; c < NCT; ++c) acc[c] = 0.f;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int k = 4 * lane + 128 * u;
+      if (k < K) {
+#pragma unroll
+        for (int c = 0; c < NCT; ++c) {
+          const float4 w4 = *reinterpret_cast<const float4*>(swT + c * K + k);
+          acc[c] += hv[u].x * w4.x + hv[u].y * w4.y + hv[u].z * w4.z + hv[u].w * w4.w;
+        }
+      }
+    }
+    for (int kb = 512; kb < K; kb += 128) {            // K > 512: the rest of the row, one chunk at a time
+      const int k = kb + 4 * lane;
+      if (k < K) {
+        const float4 h4 = *reinterpret_cast<const float4*>(h + (int64_t)my_row * K + k);
+#pragma unroll
+        for (int c = 0; c < NCT; ++c) {
+          const float4 w4 = *reinterpret_cast<const float4*>(swT + c * K + k);
+          acc[c] += h4.x * w4.x + h4.y * w4.y + h4.z * w4.z + h4.w * w4.w;
         }
       }
     }
     float z = -INFINITY;
 #pragma unroll
-    for (int c = 0; c < 16; ++c) {
+    for (int c = 0; c < NCT; ++c) {
       float v = acc[c];
+#pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == c && c < NC) z = v + bias[c];
+      if (lane == c && c < NC) z = v + bz;
     }
     float mx = z;
     int am = lane;
+#pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const float om = __shfl_xor_sync(0xffffffffu, mx, o);
       const int oa = __shfl_xor_sync(0xffffffffu, am, o);
@@ -499,54 +572,98 @@ __global__ void __launch_bounds__(256) fc3_fused_kernel(const float* __restrict_
     }
     const float e = (lane < NC) ? __expf(z - mx) : 0.f;
     float se = e;
+#pragma unroll
     for (int o = 16; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
-    const int lab = labels[row];
-    if (lane < NC) sdl[row * NC + lane] = (e / se - (lane == lab ? 1.f : 0.f)) * scale;
+    if (lane < NCT) {
+      const float d = lane < NC ? (e / se - (lane == lab ? 1.f : 0.f)) * scale : 0.f;
+      const uint32_t a = smem_u32(sdl) + (uint32_t)((my_row * NCT + lane) * 4);
+#pragma unroll
+      for (int pr = 0; pr < kFc3Cluster; ++pr) st_dsmem_f32(cluster_map_shared(a, (uint32_t)pr), d);
+    }
     const float zl = __shfl_sync(0xffffffffu, z, lab);
-    if (lane == 0) { loss_acc += logf(se) + mx - zl; correct_acc += (am == lab) ? 1u : 0u; }
-  }
-  if (blockIdx.x == 0 && lane == 0) {
-    atomicAdd(&st->loss_sum, loss_acc);
-    if (correct_acc) atomicAdd(&st->correct, correct_acc);
-  }
-  __syncthreads();
-  // ---- phase 2: dW[k, c], db[c], dh[r, k] (+ column sums of dh = bias gradient of the previous layer)
-  const int c = lane, kk = warp;
-  if (c < NC) {
-    for (int ks = kk; ks < 32; ks += nwarps) {
-      const int k = k0 + ks;
-      if (k >= K) break;
-      float s2 = 0.f;
-      for (int r = 0; r < B; ++r) s2 += sh[r * 32 + ks] * sdl[r * NC + c];
-      dw[(int64_t)k * NC + c] += s2;
-    }
-    if (blockIdx.x == 0 && kk == 0) {
-      float s2 = 0.f;
-      for (int r = 0; r < B; ++r) s2 += sdl[r * NC + c];
-      db[c] += s2;
+    if (lane == 0) {
+      atomicAdd(&st->loss_sum, logf(se) + mx - zl);
+      if (am == lab) atomicAdd(&st->correct, 1u);
     }
   }
-  float colsum = 0.f;
-  for (int t = threadIdx.x; t < B * 32; t += blockDim.x) {
-    const int r = t >> 5, ks = t & 31, k = k0 + ks;
-    if (k >= K) continue;
+  DDL_STAMP(5);
+#pragma unroll
+  for (int u = 0; u < kHs; ++u) {
+    const int o4 = u * kFc3Threads + t;
+    if (o4 < nslice4) {
+      float* d = shs + (o4 / ks4) * (KS + 1) + 4 * (o4 % ks4);
+      d[0] = hs[u].x; d[1] = hs[u].y; d[2] = hs[u].z; d[3] = hs[u].w;
+    }
+  }
+  for (int o4 = kHs * kFc3Threads + t; o4 < nslice4; o4 += kFc3Threads) {     // beyond the register-staged batches
+    const int r = o4 / ks4, k = k0 + 4 * (o4 % ks4);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k < K) v = *reinterpret_cast<const float4*>(h + (int64_t)r * K + k);
+    float* d = shs + r * (KS + 1) + 4 * (o4 % ks4);
+    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+  }
+  DDL_STAMP(6);
+  cluster_arrive_release();                  // every CTA's dlogits have landed in every sdl; shs / scol complete
+  cluster_wait_acquire();
+  DDL_STAMP(7);
+  // ---- phase 2: backward of my k-columns.  KS is a power of two in [32, 256]: t -> (ks, group) without divisions.
+  const int ks = t & (KS - 1), grp = t / KS, ngrp = kFc3Threads / KS;
+  const int k = k0 + ks;
+  {  // dW3[k, c] += sum_r h[r, k] dl[r, c]: group = (column quarter, row partition)
+    constexpr int CQ = NCT / 4;
+    const int cq = grp & 3, rp = grp >> 2, nrp = ngrp >> 2;
+    float a[CQ];
+#pragma unroll
+    for (int j = 0; j < CQ; ++j) a[j] = 0.f;
+    for (int r = rp; r < B; r += nrp) {
+      const float hval = shs[r * (KS + 1) + ks];
+#pragma unroll
+      for (int j = 0; j < CQ; ++j) a[j] += hval * sdl[r * NCT + cq * CQ + j];
+    }
+    if (k < K) {
+#pragma unroll
+      for (int j = 0; j < CQ; ++j)
+        if (cq * CQ + j < NC) atomicAdd(dw + (int64_t)k * NC + cq * CQ + j, a[j]);
+    }
+  }
+  DDL_STAMP(8);
+  if (crank == 0 && warp < NC) {             // db3[c] += sum_r dl[r, c]: warp c, lanes over rows
     float s2 = 0.f;
-    for (int cc = 0; cc < NC; ++cc) s2 += sdl[r * NC + cc] * sw3[k * NC + cc];
-    const uint32_t e = (uint32_t)(r * K + k);
-    const bool keep = thresh24 >= (1u << 24) || ddl_dropout_keep(seed, stream, e, thresh24);
-    const float o = keep ? s2 * inv_keep : 0.f;
-    dh[(int64_t)r * K + k] = o;
-    colsum += o;
+    for (int r = lane; r < B; r += 32) s2 += sdl[r * NCT + warp];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    if (lane == 0) atomicAdd(db + warp, s2);
   }
-  if (dbh) {
-    colred[warp][lane] = colsum;
-    __syncthreads();
-    if (threadIdx.x < 32 && k0 + threadIdx.x < K) {
-      float t2 = 0.f;
-      for (int l = 0; l < nwarps; ++l) t2 += colred[l][threadIdx.x];
-      dbh[k0 + threadIdx.x] += t2;
+  DDL_STAMP(9);
+  {  // dh2[r, k] = (sum_c dl[r, c] W3[k, c]) * mask / keep: a thread keeps W3[k, :] in registers and walks rows
+    float wk[NCT];
+#pragma unroll
+    for (int c = 0; c < NCT; ++c) wk[c] = k < K ? swT[c * K + k] : 0.f;
+    float colsum = 0.f;
+    for (int r = grp; r < B; r += ngrp) {
+      float s2 = 0.f;
+#pragma unroll
+      for (int c4 = 0; c4 < NCT; c4 += 4) {
+        const float4 d4 = *reinterpret_cast<const float4*>(sdl + r * NCT + c4);       // broadcast
+        s2 += d4.x * wk[c4] + d4.y * wk[c4 + 1] + d4.z * wk[c4 + 2] + d4.w * wk[c4 + 3];
+      }
+      if (k < K) {
+        const uint32_t e = (uint32_t)(r * K + k);
+        const bool keep = thresh24 >= (1u << 24) || ddl_dropout_keep(seed, stream, e, thresh24);
+        const float v = keep ? s2 * inv_keep : 0.f;
+        dh[(int64_t)r * K + k] = v;
+        colsum += v;
+      }
     }
+    if (dbh && colsum != 0.f) atomicAdd(scol + ks, colsum);
   }
+  DDL_STAMP(10);
+  if (dbh) {
+    __syncthreads();
+    for (int i = t; i < KS; i += kFc3Threads)
+      if (k0 + i < K && scol[i] != 0.f) atomicAdd(dbh + k0 + i, scol[i]);
+  }
+  DDL_STAMP(11);
 }
 
 __global__ void accuracy_kernel(const float* __restrict__ logits, const int* __restrict__ labels,
@@ -678,22 +795,52 @@ int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, f
   return fc3_bwd_launch(h, w, dl, dw, db, dh, dbh, B, K, NC, 0, stream_off, st, keep_prob, s);
 }
 
+static int fc3_fused_ks(int K) {
+  int ks = 32;
+  while (ks * kFc3Cluster < K) ks <<= 1;
+  return ks;
+}
+
+static size_t fc3_fused_smem(int B, int K, int NC) {
+  const int nct = NC <= 12 ? 12 : 16, KS = fc3_fused_ks(K);
+  return ((size_t)K * nct + (size_t)B * nct + (size_t)B * (KS + 1) + KS) * sizeof(float);
+}
+
+/* 1 when ddl_fc3_fused_st can run this shape (shared memory, one row per warp, k-slice a power of two <= 256) */
+int ddl_fc3_fused_fits(int B, int K, int NC) {
+  if (NC > 16 || NC < 1 || K % 4 || B > 32 * kFc3Cluster || K > 256 * kFc3Cluster) return 0;
+  return fc3_fused_smem(B, K, NC) <= 200 * 1024 ? 1 : 0;
+}
+
 int ddl_fc3_fused_st(const float* h, const float* w, const float* bias, const int* labels, float* dw, float* db,
                      float* dh, float* dbh, DdlStepState* st, int B, int K, int NC, float scale, uint32_t stream_off,
                      float keep_prob, cudaStream_t s) {
-  DDL_REQUIRE(NC <= 16 && st != nullptr && labels != nullptr, "ddl_fc3_fused_st: NC <= 16, st and labels required");
-  const size_t smem = ((size_t)K * NC + (size_t)B * NC + (size_t)B * 32) * sizeof(float);
-  DDL_REQUIRE(smem <= 200 * 1024, "ddl_fc3_fused_st: K=%d, B=%d do not fit shared memory", K, B);
-  if (smem > 48 * 1024) {
-    static bool attr_done = false;
-    if (!attr_done) {
-      DDL_CHECK_CUDA(cudaFuncSetAttribute(fc3_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr_done = true;
-    }
+  DDL_REQUIRE(st != nullptr && labels != nullptr, "ddl_fc3_fused_st: st and labels required");
+  DDL_REQUIRE(ddl_fc3_fused_fits(B, K, NC), "ddl_fc3_fused_st: shape B=%d K=%d NC=%d does not fit (see ddl_fc3_fused_fits)", B, K, NC);
+  const int KS = fc3_fused_ks(K);
+  const size_t smem = fc3_fused_smem(B, K, NC);
+  static bool attr_done = false;
+  if (!attr_done) {
+    DDL_CHECK_CUDA(cudaFuncSetAttribute(fc3_cluster_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DDL_CHECK_CUDA(cudaFuncSetAttribute(fc3_cluster_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_done = true;
   }
   const uint32_t thresh = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
-  DDL_LAUNCH(fc3_fused_kernel, (K + 31) / 32, 256, smem, s, h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, scale,
-             stream_off, thresh, keep_prob >= 1.f ? 1.f : 1.f / keep_prob);
+  const float inv_keep = keep_prob >= 1.f ? 1.f : 1.f / keep_prob;
+  if (NC <= 12)
+    DDL_CHECK_CUDA(ddl::launch(fc3_cluster_kernel<12>, dim3(1, 1, kFc3Cluster), dim3(kFc3Threads), smem, s, (unsigned)kFc3Cluster,
+                               h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, KS, scale, stream_off, thresh, inv_keep));
+  else
+    DDL_CHECK_CUDA(ddl::launch(fc3_cluster_kernel<16>, dim3(1, 1, kFc3Cluster), dim3(kFc3Threads), smem, s, (unsigned)kFc3Cluster,
+                               h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, KS, scale, stream_off, thresh, inv_keep));
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+/* perf experiments: enable / read the globaltimer stamps of fc3_cluster_kernel */
+int ddl_debug_stamps(int on, unsigned long long* out, int n) {
+  DDL_CHECK_CUDA(cudaMemcpyToSymbol(g_stamps_on, &on, sizeof(int)));
+  if (out && n > 0) DDL_CHECK_CUDA(cudaMemcpyFromSymbol(out, g_stamps, sizeof(unsigned long long) * (n > 32 ? 32 : n)));
   return 0;
 }
 

@@ -382,11 +382,10 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   DDL_CHECK_CUDA(cudaMemsetAsync(c.grads, 0, (size_t)c.arena_elems * sizeof(float), s));
   if (forward(e, fp, x, B, true, s)) return -1;
   const int vf = 2 * e->nconv;
-  // fc3 forward + loss + fc3 backward in one kernel; it also emits the fc2 bias gradient (column sums of dh2)
-  // (measured: the single-kernel version is 3x SLOWER - 112 us vs 15 + 22 us - because every block walks all
-  //  B rows with 8 warps instead of one warp per row across 13 blocks; kept behind DDL_FC3_FUSED for study)
-  static const bool fc3_fused = getenv("DDL_FC3_FUSED") != nullptr;
-  if (fc3_fused && (size_t)(e->F[2] * e->F[3] + B * (e->F[3] + 32)) * sizeof(float) <= 200 * 1024) {
+  // fc3 forward + loss + fc3 backward in one cluster kernel (also emits the fc2 bias gradient = column sums of dh2);
+  // DDL_FC3_SPLIT=1 or a shape that does not fit: the two separate kernels
+  static const bool fc3_split = getenv("DDL_FC3_SPLIT") != nullptr;
+  if (!fc3_split && ddl_fc3_fused_fits(B, e->F[2], e->F[3])) {
     if (ddl_fc3_fused_st(e->h2, e->P(vf + 4), e->P(vf + 5), y, e->G(vf + 4), e->G(vf + 5), e->dh2, e->G(vf + 3), c.st, B,
                          e->F[2], e->F[3], 1.f / (float)B, 1, c.keep_prob, s)) return -1;
   } else {

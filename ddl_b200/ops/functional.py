@@ -213,6 +213,21 @@ def fc3_bwd(h: torch.Tensor, w: torch.Tensor, dl: torch.Tensor, seed: int = 0, s
     return dw, db, dh
 
 
+def fc3_fused(h: torch.Tensor, w: torch.Tensor, b: torch.Tensor, labels: torch.Tensor, st: torch.Tensor,
+              keep_prob: float = 1.0, stream_off: int = 1):
+    """fc3 forward + softmax-xent + fc3 backward in one cluster kernel; returns (dw, db, dh, dbh); loss / correct are
+    added to the device step state ``st``."""
+    B, K = h.shape
+    NC = w.shape[1]
+    dw = torch.zeros(K, NC, device=h.device); db = torch.zeros(NC, device=h.device)
+    dh = torch.empty(B, K, device=h.device); dbh = torch.zeros(K, device=h.device)
+    native.check(native.lib().ddl_fc3_fused_st(native.ptr(h), native.ptr(w), native.ptr(b), native.ptr(labels), native.ptr(dw),
+                                               native.ptr(db), native.ptr(dh), native.ptr(dbh), st.data_ptr(), B, K, NC,
+                                               1.0 / B, stream_off, keep_prob, native.stream_ptr()), "ddl_fc3_fused_st")
+    native.count()
+    return dw, db, dh, dbh
+
+
 def colsum(x: torch.Tensor) -> torch.Tensor:
     out = torch.zeros(x.shape[1], device=x.device, dtype=torch.float32)
     native.check(native.lib().ddl_colsum(native.ptr(x), native.ptr(out), x.shape[0], x.shape[1], native.stream_ptr()),

@@ -105,6 +105,8 @@ def lib() -> C.CDLL:
         "ddl_fc3_xent_fwd": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, vp], i32),
         "ddl_fc3_bwd": ([vp, vp, vp, vp, vp, vp, i32, i32, i32, u32, u32, f32, vp], i32),
         "ddl_fc3_bwd_st": ([vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, u32, f32, vp], i32),
+        "ddl_fc3_fused_st": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, f32, u32, f32, vp], i32),
+        "ddl_fc3_fused_fits": ([i32, i32, i32], i32),
         "ddl_accuracy": ([vp, vp, vp, i32, i32, vp], i32),
         "ddl_tc_plan_act": ([i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, f32, vp, u32, f32, vp, vp], vp),
         "ddl_tc_plan_wgrad": ([vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),

@@ -73,10 +73,15 @@ int ddl_fc3_bwd(const float* h, const float* w, const float* dl, float* dw, floa
 int ddl_fc3_bwd_st(const float* h, const float* w, const float* dl, float* dw, float* db, float* dh, float* dbh,
                    int B, int K, int NC, const DdlStepState* st, uint32_t stream_off, float keep_prob,
                    cudaStream_t s);
-/* training path: fc3 forward + softmax-xent + fc3 backward (+ fc2 bias gradient) in one launch */
+/* training path: fc3 forward + softmax-xent + fc3 backward (+ fc2 bias gradient) in ONE launch of a thread-block
+ * cluster of 8 CTAs (model.py:85-92 forward, the matching gradients of model.py:101): each CTA computes the dlogits of
+ * its rows and stores them into every CTA's shared memory (distributed shared memory), then owns K/8 columns of the
+ * backward.  dw / db / dbh are accumulated (+=).  W3, bias and labels are read before griddepcontrol.wait: they must
+ * not be outputs of the kernel launched just before this one.  ddl_fc3_fused_fits() tells whether a shape fits. */
 int ddl_fc3_fused_st(const float* h, const float* w, const float* bias, const int* labels, float* dw, float* db,
                      float* dh, float* dbh, DdlStepState* st, int B, int K, int NC, float scale, uint32_t stream_off,
                      float keep_prob, cudaStream_t s);
+int ddl_fc3_fused_fits(int B, int K, int NC);
 int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int B, int NC, cudaStream_t s);
 
 /* ---- tcgen05 implicit-GEMM plans (csrc/tc_gemm.cu) ------------------------------------------

@@ -253,6 +253,35 @@ def test_fc3_softmax_xent_and_backward():
     assert rel_err(dw, w.grad) < 1e-4 and rel_err(db, b.grad) < 1e-4 and rel_err(dh, h.grad) < 1e-4
 
 
+@pytest.mark.parametrize("B,Kin,keep", [(100, 512, 1.0), (100, 512, 0.5), (37, 512, 0.5), (128, 1024, 0.5), (100, 200, 1.0)])
+def test_fc3_fused_cluster_kernel(B, Kin, keep):
+    """fc3 forward + loss + backward in one 8-CTA cluster kernel (dlogits exchanged through distributed shared memory)."""
+    from ddl_b200.ops import functional as K, native
+    from ddl_b200.models.oracle import dropout_keep_mask
+    torch.manual_seed(8)
+    NC = 10
+    h = torch.randn(B, Kin, device=dev(), requires_grad=True)
+    w = (torch.randn(Kin, NC, device=dev()) * 0.1).requires_grad_(True)
+    b = torch.randn(NC, device=dev(), requires_grad=True)
+    y = torch.randint(0, NC, (B,), device=dev(), dtype=torch.int32)
+    st = native.new_step_state(seed=21)
+    st[5] = 4                                   # stream of this step; the kernel adds stream_off = 1
+    mask = dropout_keep_mask(21, 5, B * Kin, keep, dev()).view(B, Kin) if keep < 1 else torch.ones(B, Kin, device=dev(), dtype=torch.bool)
+    hd = h * mask / keep                        # h is the dropped-out activation's input: dh gets the mask
+    logits_ref = hd @ w + b
+    loss = F.cross_entropy(logits_ref, y.long())
+    loss.backward()
+    # the kernel sees the already-dropped activation and masks the gradient it returns
+    dw, db, dh, dbh = K.fc3_fused(hd.detach().contiguous(), w.detach(), b.detach(), y, st, keep_prob=keep)
+    s = native.read_step_state(st)
+    assert abs(s["loss_sum"] / B - float(loss)) < 1e-4
+    assert s["correct"] == int((logits_ref.argmax(1) == y.long()).sum())
+    assert rel_err(dw, w.grad) < 1e-4 and rel_err(db, b.grad) < 1e-4
+    assert rel_err(dh, h.grad) < 1e-4
+    assert torch.equal(dh == 0, ~mask | (h.grad == 0))
+    assert rel_err(dbh, h.grad.sum(0)) < 1e-4
+
+
 def _engine_setup(batch=100, keep_prob=0.5, seed=5, wm=1):
     from ddl_b200.config import Config
     from ddl_b200.models import make_spec, oracle
