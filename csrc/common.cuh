@@ -37,6 +37,11 @@ const char* get_error();
 
 namespace ddl {
 bool pdl_enabled();        // DDL_PDL=0 disables programmatic dependent launch
+// The next launch of this thread carries no programmatic-serialization attribute: it starts only after everything
+// before it in its stream has completed.  Used for the first kernel of a forward pass: later kernels prefetch their
+// weight operands BEFORE griddepcontrol.wait, which is only sound if no earlier kernel that writes weights (the
+// optimizer / pull of the previous step) can still be running - this cuts the chain of early launches there.
+void no_pdl_once();
 // one launch path for every kernel: PDL attribute (+ optional cluster along z)
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,

@@ -76,7 +76,10 @@ struct DdlEngine {
   // one stream per conv weight-gradient kernel: they only depend on their own dY, and serialising them on one
   // stream made that stream the critical path of the backward (tools/timeline.py)
   cudaStream_t wside[2] = {nullptr, nullptr};       // conv3 / conv2 wgrads (conv4 + FC wgrads stay on `side`)
-  cudaEvent_t ev_wjoin[2] = {nullptr, nullptr}, ev_w0 = nullptr, ev_main2 = nullptr;
+  cudaEvent_t ev_wjoin[2] = {nullptr, nullptr}, ev_w0 = nullptr, ev_main2 = nullptr, ev_pre0 = nullptr, ev_pre1 = nullptr;
+  bool own_advance = false;                         // the engine launches ddl_step_advance itself (side stream)
+  float adv_lr = 0.f, adv_b1 = 0.f, adv_b2 = 0.f;
+  int adv_opt = 1;
 
   const float* P(int v) const { return cfg.params + cfg.var_offset[v]; }
   float* G(int v) const { return cfg.grads + cfg.var_offset[v]; }
@@ -266,8 +269,9 @@ FwdPlans* get_fwd(DdlEngine* e, int B, bool train) {
 }
 
 // forward through fc2; x [B,784].  Writes pooled[], idx[] (train), h1, h2.
-int forward(DdlEngine* e, FwdPlans* fp, const float* x, int B, bool train, cudaStream_t s) {
+int forward(DdlEngine* e, FwdPlans* fp, const float* x, int B, bool train, cudaStream_t s, cudaEvent_t before_fc = nullptr) {
   int v = 0;
+  ddl::no_pdl_once();        // first kernel of the pass: full dependency on whatever updated the weights before it
   if (e->nconv) {
     if (ddl_conv1_relu_pool(x, e->P(0), e->P(1), e->pooled[0], train ? e->idx[0] : nullptr, B, e->S[0], e->C[1], s))
       return -1;
@@ -283,7 +287,10 @@ int forward(DdlEngine* e, FwdPlans* fp, const float* x, int B, bool train, cudaS
       if (ddl_tc_plan_run(fp->conv[l - 1], s)) return -1;
       if (ddl_maxpool_fwd(e->raw, e->P(v + 1), e->pooled[l], train ? e->idx[l] : nullptr, B, S, S, cout, s)) return -1;
     }
+    if (before_fc) DDL_CHECK_CUDA(cudaStreamWaitEvent(s, before_fc, 0));    // dropout reads the step state
     if (ddl_tc_plan_run(fp->fc[0], s)) return -1;
+  } else if (before_fc) {
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(s, before_fc, 0));
   }
   if (ddl_tc_plan_run(fp->fc[1], s)) return -1;
   return 0;
@@ -336,7 +343,9 @@ DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg) {
     if (cudaEventCreateWithFlags(&e->ev_wjoin[i], cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   }
   if (cudaEventCreateWithFlags(&e->ev_w0, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&e->ev_main2, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
+      cudaEventCreateWithFlags(&e->ev_main2, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_pre0, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_pre1, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   if (alloc(e, (void**)&e->h1, mb * e->F[1] * 4) || alloc(e, (void**)&e->h2, mb * e->F[2] * 4) ||
       alloc(e, (void**)&e->dh1, (size_t)cfg->batch * e->F[1] * 4) || alloc(e, (void**)&e->dh2, (size_t)cfg->batch * e->F[2] * 4) ||
       alloc(e, (void**)&e->logits, mb * 16 * 4) || alloc(e, (void**)&e->dlogits, (size_t)cfg->batch * 16 * 4) ||
@@ -369,6 +378,8 @@ void ddl_engine_destroy(DdlEngine* e) {
   }
   if (e->ev_w0) cudaEventDestroy(e->ev_w0);
   if (e->ev_main2) cudaEventDestroy(e->ev_main2);
+  if (e->ev_pre0) cudaEventDestroy(e->ev_pre0);
+  if (e->ev_pre1) cudaEventDestroy(e->ev_pre1);
   delete e;
 }
 
@@ -379,8 +390,14 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   const int B = c.batch;
   FwdPlans* fp = get_fwd(e, B, true);
   DDL_REQUIRE(fp != nullptr, "ddl_engine_train_step: no forward plans");
-  DDL_CHECK_CUDA(cudaMemsetAsync(c.grads, 0, (size_t)c.arena_elems * sizeof(float), s));
-  if (forward(e, fp, x, B, true, s)) return -1;
+  // the step-state advance (when the engine owns it) and the zeroing of the gradient arena run on the side stream
+  // beside conv1..conv4; the first consumers are fc1 (dropout stream / seed) and the fc3 kernel (first gradient)
+  DDL_CHECK_CUDA(cudaEventRecord(e->ev_pre0, s));
+  DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side, e->ev_pre0, 0));
+  if (e->own_advance && ddl_step_advance(c.st, e->adv_lr, e->adv_b1, e->adv_b2, e->adv_opt, e->side)) return -1;
+  DDL_CHECK_CUDA(cudaMemsetAsync(c.grads, 0, (size_t)c.arena_elems * sizeof(float), e->side));
+  DDL_CHECK_CUDA(cudaEventRecord(e->ev_pre1, e->side));
+  if (forward(e, fp, x, B, true, s, e->ev_pre1)) return -1;
   const int vf = 2 * e->nconv;
   // fc3 forward + loss + fc3 backward in one cluster kernel (also emits the fc2 bias gradient = column sums of dh2);
   // DDL_FC3_SPLIT=1 or a shape that does not fit: the two separate kernels
@@ -467,6 +484,13 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     }
   }
   if (e->ov_n > 0) DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join2, 0));
+  return 0;
+}
+
+int ddl_engine_set_advance(DdlEngine* e, float lr, float b1, float b2, int advance_opt) {
+  DDL_REQUIRE(e != nullptr, "ddl_engine_set_advance: null engine");
+  e->own_advance = true;
+  e->adv_lr = lr; e->adv_b1 = b1; e->adv_b2 = b2; e->adv_opt = advance_opt;
   return 0;
 }
 

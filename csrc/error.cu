@@ -13,8 +13,11 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* get_error() { return g_err; }
+static thread_local bool g_no_pdl_once = false;
+void no_pdl_once() { g_no_pdl_once = true; }
 bool pdl_enabled() {
   static const bool on = [] { const char* e = getenv("DDL_PDL"); return !(e && e[0] == '0'); }();
+  if (g_no_pdl_once) { g_no_pdl_once = false; return false; }
   return on;
 }
 }  // namespace ddl

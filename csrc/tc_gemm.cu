@@ -167,7 +167,11 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_addr;
   if (ptrace && threadIdx.x == 0) p.trace[1] = ddl_globaltimer();
-  pdl_wait();                              // everything above overlapped the previous kernel; its data is needed from here
+  // everything above overlapped the previous kernel; its data (the activation operand) is needed from here.  The
+  // weight operand is not produced by the preceding kernels (see ddl::no_pdl_once), so the B producer (warp 3) starts
+  // filling the pipeline right away and only joins the wait before its epilogue duty.
+  const bool early_b = !p.pull;
+  if (!(early_b && warp == 3)) pdl_wait();
   if (ptrace && threadIdx.x == 0) p.trace[2] = ddl_globaltimer();
 
   if (warp == 2 && store_through) {
@@ -217,6 +221,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
       if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
   }
+  if (early_b && warp == 3) pdl_wait();
 
   if (warp == 0) {
     // ================= TMA producer (warp-uniform loop, one elected lane issues) =================

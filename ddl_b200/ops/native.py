@@ -131,6 +131,7 @@ def lib() -> C.CDLL:
         "ddl_engine_create": ([C.POINTER(EngineCfg)], vp),
         "ddl_engine_destroy": ([vp], None),
         "ddl_engine_train_step": ([vp, vp, vp, vp], i32),
+        "ddl_engine_set_advance": ([vp, f32, f32, f32, i32], i32),
         "ddl_engine_set_overlap": ([vp, C.POINTER(Comm), vp, i32, i32], i32),
         "ddl_engine_eval": ([vp, vp, vp, i32, vp, vp, vp], i32),
         "ddl_engine_buffer": ([vp, i32], vp),

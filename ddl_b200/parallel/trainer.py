@@ -121,6 +121,8 @@ class SPMDTrainer:
                            fc_w_src=getattr(self.transport, "k4_src", None)) if lay.is_worker else None
         if self.model is not None and self.model.backend == "native" and hasattr(self.transport, "attach_engine"):
             self.transport.attach_engine(self.model.impl)
+        # the native engine (once attached to the fused transport) launches the step-state advance itself
+        self._begin_kw = {"engine": True} if (self.model is not None and getattr(self.transport, "engine_advances", False)) else {}
         self.transport.initial_sync()
         if lay.is_worker:
             self.x_test = self.data.x_test.to(self.device)
@@ -157,7 +159,7 @@ class SPMDTrainer:
         if self._graph is not None:
             return self._graph_step(cnt)
         loss = None
-        self.transport.begin_step()
+        self.transport.begin_step(**self._begin_kw)
         if lay.is_worker:
             b, e = self.data.batch_slice(cnt, cfg.batch_size, lay.my_worker, lay.num_workers,
                                          cfg.replicate_data)
@@ -177,35 +179,69 @@ class SPMDTrainer:
                 and (self.model is None or self.model.backend == "native") and not self.cfg.profile)
 
     def _capture(self) -> None:
-        """Capture [step-state advance, forward, backward, push+update+pull] once; every later step
-        is one H2D copy pair + one graph launch (phases are 10-100 us, launch
-        latency would dominate otherwise)."""
+        """Capture [step-state advance, forward, backward, push+update+pull] once per input slot; every later step
+        is one graph launch, and the H2D copy of the NEXT batch (pinned host memory -> the other slot, on a copy
+        stream) runs underneath it (phases are 10-100 us, launch latency and the ~20 us of
+        serialized H2D + launch gaps would dominate otherwise)."""
         cfg, lay = self.cfg, self.layout
+        nslots = 2 if lay.is_worker else 1
         if lay.is_worker:
-            self._x_static = torch.zeros(cfg.batch_size, 784, device=self.device)
-            self._y_static = torch.zeros(cfg.batch_size, dtype=torch.int32, device=self.device)
+            self._x_slot = [torch.zeros(cfg.batch_size, 784, device=self.device) for _ in range(nslots)]
+            self._y_slot = [torch.zeros(cfg.batch_size, dtype=torch.int32, device=self.device) for _ in range(nslots)]
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            self._ev_ready = [torch.cuda.Event() for _ in range(nslots)]     # slot filled by the copy stream
+            self._ev_free = [torch.cuda.Event() for _ in range(nslots)]      # slot's last consumer (a graph replay) enqueued
+            self._slot_cnt = [None] * nslots                                 # batch index prefetched into each slot
+            self._slot = 0
+            self._nb_local = max(1, self.data.batches_per_epoch(cfg.batch_size, lay.num_workers, cfg.replicate_data))
         torch.cuda.synchronize()
         from ..ops import native
-        l0 = native.LAUNCHES
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            self.transport.begin_step()
-            if lay.is_worker:
-                self.model.impl.enqueue_train_step(self._x_static, self._y_static)
-            self.transport.step()
-        self._graph = g
-        self.launches_per_step = native.LAUNCHES - l0      # kernels of ours inside one replay
-        # the capture itself did not execute anything; global_step is untouched
+        self._graphs = []
+        for slot in range(nslots):
+            l0 = native.LAUNCHES
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.transport.begin_step(**self._begin_kw)
+                if lay.is_worker:
+                    self.model.impl.enqueue_train_step(self._x_slot[slot], self._y_slot[slot])
+                self.transport.step()
+            self._graphs.append(g)
+            if slot == 0:
+                self.launches_per_step = native.LAUNCHES - l0      # kernels of ours inside one replay
+        self._graph = self._graphs[0]
+        # the captures themselves did not execute anything; global_step is untouched
+
+    def _h2d(self, slot: int, cnt: int) -> None:
+        cfg, lay = self.cfg, self.layout
+        b, e = self.data.batch_slice(cnt, cfg.batch_size, lay.my_worker, lay.num_workers, cfg.replicate_data)
+        self._x_slot[slot].copy_(self.data.x_train[b:e], non_blocking=True)
+        self._y_slot[slot].copy_(self.data.y_train[b:e], non_blocking=True)
 
     def _graph_step(self, cnt: int) -> Optional[torch.Tensor]:
         cfg, lay = self.cfg, self.layout
-        if lay.is_worker:
-            b, e = self.data.batch_slice(cnt, cfg.batch_size, lay.my_worker, lay.num_workers, cfg.replicate_data)
-            self._x_static.copy_(self.data.x_train[b:e], non_blocking=True)
-            self._y_static.copy_(self.data.y_train[b:e], non_blocking=True)
-        self._graph.replay()
+        if not lay.is_worker:
+            self._graphs[0].replay()
+            self.global_step += 1
+            return None
+        main = torch.cuda.current_stream()
+        slot = self._slot
+        if self._slot_cnt[slot] == cnt:
+            main.wait_event(self._ev_ready[slot])        # prefetched while the previous step ran
+        else:
+            self._h2d(slot, cnt)                          # first step / out-of-order batch index: copy in line
+        self._graphs[slot].replay()
+        self._ev_free[slot].record(main)
+        # prefetch the next batch of the epoch into the other slot, underneath this step's graph
+        nxt, nslot = (cnt + 1) % self._nb_local, slot ^ 1
+        self._copy_stream.wait_event(self._ev_free[nslot])    # its last consumer was the previous step (already enqueued)
+        with torch.cuda.stream(self._copy_stream):
+            self._h2d(nslot, nxt)
+            self._ev_ready[nslot].record(self._copy_stream)
+        self._slot_cnt[nslot] = nxt
+        self._slot_cnt[slot] = None
+        self._slot = nslot
         self.global_step += 1
-        return self.transport.loss(cfg.batch_size) if lay.is_worker else None
+        return self.transport.loss(cfg.batch_size)
 
     def evaluate(self) -> float:
         if hasattr(self.transport, "ensure_local"):

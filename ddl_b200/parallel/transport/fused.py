@@ -198,6 +198,7 @@ class FusedTransport(SpmdTransport):
         spec = params.spec
         self.bucketed = bool(cfg.overlap_push and cfg.mode == "sync" and spec.kind == "cnn")
         self.engine_overlap = False
+        self.engine_advances = False
         kind_id, step0, aa, bb, eps = FlatOptimizer(torch.zeros(1), cfg.optimizer, cfg.lr, cfg.beta1, cfg.beta2,
                                                     cfg.eps, cfg.momentum, use_native=False).hyper(1)
 
@@ -321,8 +322,13 @@ class FusedTransport(SpmdTransport):
             torch.cuda.synchronize()
             dist.barrier()
 
-    def begin_step(self) -> None:
+    def begin_step(self, engine: bool = False) -> None:
+        """Advances the device step state.  ``engine=True``: the native engine's training step follows and (once
+        attached) launches the advance itself, beside its convolutions."""
         c = self.cfg
+        if engine and self.engine_advances:
+            native.count()
+            return
         native.check(self.L.ddl_step_advance(self.st.data_ptr(), c.lr, c.beta1, c.beta2,
                                              1 if c.mode == "sync" else 0, self._s()), "ddl_step_advance")
         native.count()
@@ -331,6 +337,10 @@ class FusedTransport(SpmdTransport):
         """Hand bucket 0 to the native engine: it launches those push/update/pull kernels on its side stream in
         the middle of the backward (as soon as conv3..fc3 gradients exist), overlapping them with the conv2 /
         conv1 backward - SURVEY 7.2 step 7, "backward-overlapped push"."""
+        c = self.cfg
+        native.check(self.L.ddl_engine_set_advance(backend.h, c.lr, c.beta1, c.beta2, 1 if c.mode == "sync" else 0),
+                     "ddl_engine_set_advance")
+        self.engine_advances = True
         if not (self.bucketed and self.early_args):
             return
         arr = (native.SyncArgs * len(self.early_args))(*self.early_args)

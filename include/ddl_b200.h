@@ -96,6 +96,11 @@ int ddl_accuracy(const float* logits, const int* labels, unsigned* correct, int 
  * (ddl_tc_plan_needs_zero() returns 1).  ksplit in [2,8] WITH epilogue flags / colsum: the split CTAs of a
  * tile form a thread-block cluster and reduce through plan-owned scratch, keeping the fused epilogue.
  * colsum (may be NULL): += per-column sums of the final output values (a bias gradient).
+ * Launch-order contract: every plan kernel starts under programmatic dependent launch and loads its WEIGHT operand
+ * (`w`) before griddepcontrol.wait, i.e. possibly while earlier kernels of the stream still run.  `w` must therefore
+ * not be written by a kernel of this library launched shortly before in the same stream without an intervening
+ * full dependency (the engine launches the first kernel of every pass without the attribute for this reason);
+ * outputs of other libraries' kernels (no early-launch trigger) are always safe.
  * w_store_dst (may be NULL; fprop only) - K4, the pull fused into the consumer GEMM: `w` may then point
  * into ANOTHER rank's parameter arena (a peer-mapped pointer): the weight tiles are TMA-loaded over
  * NVLink straight into the MMA's shared-memory stage and written through to w_store_dst (this rank's
@@ -230,6 +235,10 @@ DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg);
 void ddl_engine_destroy(DdlEngine* e);
 /* sess.run(self.grads, keep_prob=.5) (mnist_sync/worker.py:30): x [B,784], y [B] class ids */
 int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream_t s);
+/* After this call ddl_engine_train_step launches ddl_step_advance(st, lr, b1, b2, advance_opt) itself, on its side
+ * stream beside the convolutions (the first reader of the step state is fc1's dropout); the caller must then NOT
+ * advance the state before the step. */
+int ddl_engine_set_advance(DdlEngine* e, float lr, float b1, float b2, int advance_opt);
 /* Backward-overlapped push: the engine launches ddl_sync_push_update_pull for these argument blocks on its
  * side stream as soon as the gradients of conv3..fc3 (98% of the bytes) are complete, while the main stream
  * still runs the conv2 / conv1 backward.  The caller launches the remaining bucket after the step. */
