@@ -29,6 +29,11 @@ namespace {
 
 constexpr int kCommThreads = 512;
 
+// perf experiments: globaltimer stamps of block 0 / thread 0 of the sync kernel (tools/sync_phase.py)
+__device__ int g_cstamps_on = 0;
+__device__ unsigned long long g_cstamps[16];
+#define DDL_CSTAMP(i) do { if (cst) g_cstamps[i] = ddl_globaltimer(); } while (0)
+
 DDL_DEVICE float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
 
 // all ranks: write `epoch` into slot [me] of every peer's pad, then wait until every slot of my own
@@ -104,16 +109,22 @@ __global__ void __launch_bounds__(kCommThreads)
 sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
   pdl_enter();
   __shared__ uint32_t s_last;
+  const bool cst = g_cstamps_on && blockIdx.x == 0 && threadIdx.x == 0 && a.bucket == 0;
+  DDL_CSTAMP(0);
   const uint32_t t = a.st->t;                       // same on every rank: all ranks advance together
   const uint32_t nb = a.nbuckets > 1 ? (uint32_t)a.nbuckets : 1u;
   const uint32_t epochA = 2u * nb * t + 2u * (uint32_t)a.bucket + 1u, epochB = epochA + 1u;
-  // ---- barrier A: my gradients are complete (previous kernels on this stream) -> tell everyone
-  if (blockIdx.x == 0) {
-    __threadfence_system();
-    pad_signal(c, 0, epochA);
+  // ---- barrier A: my gradients are complete (previous kernels on this stream) -> tell everyone.
+  // The release store is the only fence needed (the explicit fence.sys in front of it cost a second ~4 us
+  // MEMBAR.SYS, tools/sync_phase.py).  A single rank has nobody to wait for: no signals, no system fences.
+  const bool solo = c.world == 1;
+  if (!solo) {
+    if (blockIdx.x == 0) pad_signal(c, 0, epochA);
+    DDL_CSTAMP(1);
+    pad_wait(c, 0, epochA);                         // every block polls its own (local) pad
+    __syncthreads();
   }
-  pad_wait(c, 0, epochA);                           // every block polls its own (local) pad
-  __syncthreads();
+  DDL_CSTAMP(2);
 
   constexpr int WCH = (U == 1) ? DDL_MAX_PEERS : 4;  // peers loaded per batch: WCH * U float4 in flight
   const float step = (KIND == 2) ? a.st->lr_t : a.lr;
@@ -204,18 +215,26 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
   // One fence per block, not per thread: bar.sync makes the block's stores observed by thread 0, whose
   // (cumulative) fence then orders them before the counter bump - the cooperative-groups grid-sync idiom.
   // A system-scope fence is only needed when stores went to peers.
+  DDL_CSTAMP(3);
+  if (solo) return;                                // the kernel boundary orders everything for the next kernel
   __syncthreads();
+  DDL_CSTAMP(4);
   if (threadIdx.x == 0) {
-    if (c.world > 1) __threadfence_system(); else __threadfence();
+    __threadfence_system();
+    DDL_CSTAMP(5);
     s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+    DDL_CSTAMP(6);
   }
   __syncthreads();
   if (s_last) {
-    if (threadIdx.x == 0) { *a.done_counter = 0; __threadfence_system(); }
+    // every block's fence + counter bump has been observed by this block's thread 0; the release stores below order
+    // them (cumulatively) before the "delivered" signal
+    if (threadIdx.x == 0) *a.done_counter = 0;
     __syncthreads();
     pad_signal(c, 0, epochB);
     pad_wait(c, 0, epochB);
   }
+  DDL_CSTAMP(7);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -357,6 +376,13 @@ int comm_grid(int64_t elems) {
 }  // namespace
 
 extern "C" {
+
+/* perf experiments: enable / read the globaltimer stamps of the sync kernel's block 0 (bucket 0) */
+int ddl_comm_stamps(int on, unsigned long long* out, int n) {
+  DDL_CHECK_CUDA(cudaMemcpyToSymbol(g_cstamps_on, &on, sizeof(int)));
+  if (out && n > 0) DDL_CHECK_CUDA(cudaMemcpyFromSymbol(out, g_cstamps, sizeof(unsigned long long) * (n > 16 ? 16 : n)));
+  return 0;
+}
 
 int ddl_dev_malloc(void** p, size_t bytes) {
   DDL_CHECK_CUDA(cudaMalloc(p, bytes));

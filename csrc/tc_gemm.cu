@@ -24,6 +24,7 @@
 
 #include <mutex>
 #include <stdlib.h>
+#include <string.h>
 #include <new>
 
 namespace {
@@ -83,6 +84,7 @@ struct WgradParams {
   int psplit;
   int stages;
   float* out;                      // [taps][cb][ca], accumulated with red.add
+  unsigned long long* trace;       // perf experiments (DDL_TC_TRACE): per-iteration clock64 stamps of CTA (0,0,0)
 };
 
 enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16, EPI_COLSUM = 32,
@@ -630,6 +632,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   const int niter = max(0, t_end - t_begin);
   const int ctot = ntap * p.ntile;                        // accumulator columns in use
   const uint32_t ncols = ctot <= 32 ? 32u : ctot <= 64 ? 64u : ctot <= 128 ? 128u : ctot <= 256 ? 256u : 512u;
+  const bool wtrace = p.trace != nullptr && blockIdx.x + blockIdx.y + blockIdx.z == 0;
+  if (wtrace && threadIdx.x == 0) p.trace[520] = clock64();
   const int a_live = min(kTileM / 32, (p.ca - a0 + 31) / 32);     // boxes that hold real channels
   const int b_live = min(b_boxes, (p.cb - b0 + 31) / 32);
 
@@ -647,31 +651,45 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   const uint32_t tmem_base = bars->tmem_addr;
   pdl_wait();                              // everything above overlapped the previous kernel; its data is needed from here
 
-  if (warp == 0) {
-    const uint32_t tx = (uint32_t)((a_live + ntap * b_live) * box_bytes);
+  // ================= TMA producers: warps 0, 2, 3, 4, 5 (the epilogue warps are idle until the accumulator is done).
+  // One UTMALDG keeps its issuing lane busy for ~290 cycles per 56-row box (tools/wgrad_trace.py): a single producer
+  // spent ~4300 cycles issuing the 15 boxes of a conv2 stage while the MMA warp needed ~1200, so the boxes of a stage
+  // are dealt round-robin to five issuing warps.  Warp 0 announces the stage's total bytes; a complete_tx that lands
+  // first just drives the count negative until then - the phase cannot complete before warp 0's arrive.
+  const int pidx = warp == 0 ? 0 : (warp >= 2 ? warp - 1 : -1);
+  if (pidx >= 0) {
+    constexpr int kProducers = 5;
+    const int nboxes = a_live + ntap * b_live;
+    const uint32_t tx = (uint32_t)(nboxes * box_bytes);
     int s = 0;
     uint32_t ph = 0;
     for (int i = 0; i < niter; ++i) {
       mbar_wait(&bars->empty[s], ph ^ 1u);
       if (elect_one()) {
+        if (wtrace && pidx == 0 && i < 64) p.trace[i * 8 + 0] = clock64();
         const int t = t_begin + i;
         const int tw = t % p.tiles_w, th = (t / p.tiles_w) % p.tiles_h, tn = t / (p.tiles_w * p.tiles_h);
         const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
         uint8_t* sa = smem + (size_t)s * stage_bytes;
         uint8_t* sb = sa + p.a_alloc * box_bytes;
-        mbar_expect_tx(&bars->full[s], tx);
-        for (int j = 0; j < a_live; ++j)
-          tma_load_4d(sa + j * box_bytes, &map_g, &bars->full[s], a0 + 32 * j, w0, h0, n0);
-        for (int tt = 0; tt < ntap; ++tt) {
-          const int tap = tap0 + tt;
-          const int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
-          for (int j = 0; j < b_live; ++j)
+        if (pidx == 0) mbar_expect_tx(&bars->full[s], tx);
+        for (int bx = pidx; bx < nboxes; bx += kProducers) {
+          if (bx < a_live) {
+            tma_load_4d(sa + bx * box_bytes, &map_g, &bars->full[s], a0 + 32 * bx, w0, h0, n0);
+          } else {
+            const int tt = (bx - a_live) / b_live, j = (bx - a_live) % b_live;
+            const int tap = tap0 + tt;
+            const int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
             tma_load_4d(sb + (tt * b_boxes + j) * box_bytes, &map_x, &bars->full[s], b0 + 32 * j, w0 + dw, h0 + dh, n0);
+          }
         }
+        if (wtrace && pidx == 0 && i < 64) p.trace[i * 8 + 1] = clock64();
       }
       __syncwarp();
       if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
+  }
+  if (warp == 0) {
   } else if (warp == 1) {
     const int ksteps = R / kUmmaK;
     const uint32_t smem_base = smem_u32(smem);
@@ -681,9 +699,11 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     int s = 0;
     uint32_t ph = 0;
     for (int i = 0; i < niter; ++i) {
+      if (wtrace && i < 64 && lane == 0) p.trace[i * 8 + 2] = clock64();
       mbar_wait(&bars->full[s], ph);
       tc_fence_after();
       if (elect_one()) {
+        if (wtrace && i < 64) p.trace[i * 8 + 3] = clock64();
         const uint32_t sa = smem_base + (uint32_t)(s * stage_bytes);
         const uint32_t sb = sa + (uint32_t)(p.a_alloc * box_bytes);
         for (int k = 0; k < ksteps; ++k) {
@@ -699,6 +719,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
         }
         umma_commit(&bars->empty[s]);
         if (i == niter - 1) umma_commit(&bars->tmem_full);
+        if (wtrace && i < 64) p.trace[i * 8 + 4] = clock64();
       }
       __syncwarp();
       if (++s == p.stages) { s = 0; ph ^= 1u; }
@@ -712,6 +733,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     if (lane == 0) mbar_wait(&bars->tmem_full, 0);
     __syncwarp();
     tc_fence_after();
+    if (wtrace && threadIdx.x == 64) p.trace[521] = clock64();
     // out[tap][b][a]: `a` (this lane's TMEM row) is the contiguous index.  A 4x4 register transpose inside
     // each quad of lanes turns 16 scalar reds per lane into 4 x red.global.add.v4.f32 on 4 consecutive a.
     const int ql = lane & 3;
@@ -745,8 +767,10 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     }
   }
   tc_fence_before();
+  if (wtrace && threadIdx.x == 64) p.trace[522] = clock64();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, ncols);
+  if (wtrace && threadIdx.x == 0) p.trace[523] = clock64();
 }
 
 // ------------------------------------------------------------------------------------------------ host
@@ -1006,7 +1030,15 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   int tpc_max = 512 / ntile;
   if (tpc_max > 1 && (256 % ntile) != 0) tpc_max = 256 / ntile > 0 ? 256 / ntile : 1;
   if (tpc_max < 1) tpc_max = 1;
-  if (getenv("DDL_WGRAD_TPC")) tpc_max = atoi(getenv("DDL_WGRAD_TPC"));
+  // Measured (tools/wgrad_perf.py, profiles/wgrad_policy.md): about five taps per CTA and one wave of CTAs is the
+  // fastest split for all three conv layers (20-25 us alone vs 31-45 us with the widest tap groups): fewer shifted X
+  // boxes per stage (deeper pipeline, larger pixel boxes) and a narrower red.add epilogue per CTA.
+  // ... but inside the training step the wider grids take SMs from the critical dgrad chain running next to them
+  // (336k vs 367k samples/s), so it is opt-in: DDL_WGRAD_POLICY=wave
+  static const bool old_policy = !(getenv("DDL_WGRAD_POLICY") && !strcmp(getenv("DDL_WGRAD_POLICY"), "wave"));
+  if (!old_policy && tpc_max > 5) tpc_max = 5;
+  if (getenv("DDL_WGRAD_TPC") && atoi(getenv("DDL_WGRAD_TPC")) >= 1 && atoi(getenv("DDL_WGRAD_TPC")) < tpc_max)
+    tpc_max = atoi(getenv("DDL_WGRAD_TPC"));
   if (tpc_max > taps) tpc_max = taps;
   p.tgroups = ceil_div(taps, tpc_max);
   p.tpc = ceil_div(taps, p.tgroups);
@@ -1014,8 +1046,10 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   p.a_alloc = a_live_max;
   if (p.a_alloc + p.tpc * b_boxes < kTileM / 32) p.a_alloc = kTileM / 32;   // the M=128 descriptor spans 4 atoms
   const int boxes = p.a_alloc + p.tpc * b_boxes;
-  // rows per stage: multiple of 8 (one UMMA K step = 8 pixel rows); two stages must fit in shared memory
-  int max_rows = ((216 * 1024 / 2) / (boxes * 128)) & ~7;
+  // rows per stage: multiple of 8 (one UMMA K step = 8 pixel rows); two stages must fit in shared memory.
+  // DDL_WGRAD_SMEM_KB (perf experiments): shared-memory budget of a wgrad CTA (default 216: one CTA per SM)
+  static const int smem_kb = getenv("DDL_WGRAD_SMEM_KB") ? atoi(getenv("DDL_WGRAD_SMEM_KB")) : 216;
+  int max_rows = ((smem_kb * 1024 / 2) / (boxes * 128)) & ~7;
   if (max_rows > 128) max_rows = 128;
   if (max_rows < 8) { delete pl; return fail("tap group does not fit in shared memory"); }
   choose_box(N, H, W, max_rows, 8, &p.bw, &p.bh, &p.bn);
@@ -1027,18 +1061,30 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   if (psplit <= 0) {
     // Every pixel split re-adds the whole dW tile with red.add, so splits are not free: aim for >= ~12
     // pixel tiles per CTA and never more than one wave of CTAs.
-    const int wave = ceil_div(148, p.tgroups * p.mtiles * p.ntiles);
-    psplit = ceil_div(ptiles, 12);
-    if (psplit > wave) psplit = wave;
+    const int groups = p.tgroups * p.mtiles * p.ntiles;
+    if (old_policy) {
+      const int wave = ceil_div(148, groups);
+      psplit = ceil_div(ptiles, 12);
+      if (psplit > wave) psplit = wave;
+    } else {
+      // one wave of CTAs, but at least ~4 pixel tiles each (every split re-adds the whole dW tile with red.add)
+      psplit = 148 / groups;
+      if (psplit > ceil_div(ptiles, 4)) psplit = ceil_div(ptiles, 4);
+    }
   }
   p.psplit = psplit < 1 ? 1 : (psplit > ptiles ? ptiles : psplit);
   const int stage_bytes = boxes * R * 128;
-  int stages = (216 * 1024) / stage_bytes;
+  int stages = (smem_kb * 1024) / stage_bytes;
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages > ceil_div(ptiles, p.psplit)) stages = ceil_div(ptiles, p.psplit) < 2 ? 2 : ceil_div(ptiles, p.psplit);
   if (stages < 1) { delete pl; return fail("stage does not fit in shared memory"); }
   p.stages = stages;
   p.out = out;
+  p.trace = nullptr;
+  if (getenv("DDL_TC_TRACE")) {
+    cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long));
+    cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
+  }
   pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
   pl->grid = dim3(p.tgroups, p.mtiles * p.ntiles, p.psplit);
   const uint64_t dg[4] = {(uint64_t)ca, (uint64_t)W, (uint64_t)H, (uint64_t)N};
@@ -1075,8 +1121,9 @@ int ddl_tc_plan_needs_zero(const DdlTcPlan* pl) { return pl && pl->kind == 0 && 
 
 /* perf experiments: copies the clock64 trace of an act plan created under DDL_TC_TRACE=1 */
 int ddl_tc_plan_trace(const DdlTcPlan* pl, unsigned long long* host_out, int n) {
-  DDL_REQUIRE(pl && pl->kind == 0 && pl->act.trace, "no trace buffer");
-  DDL_CHECK_CUDA(cudaMemcpy(host_out, pl->act.trace, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  const unsigned long long* src = pl ? (pl->kind == 0 ? pl->act.trace : pl->wg.trace) : nullptr;
+  DDL_REQUIRE(src != nullptr, "no trace buffer");
+  DDL_CHECK_CUDA(cudaMemcpy(host_out, src, (size_t)n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
   return 0;
 }
 
