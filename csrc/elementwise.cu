@@ -209,6 +209,78 @@ __global__ void __launch_bounds__(192) conv1_wgrad_kernel(const float* __restric
   }
 }
 
+// conv1 weight / bias gradient from the POOLED layout: after pool + ReLU backward only the argmax pixel of every
+// 2x2 window carries gradient, so the sum runs over B * (S/2)^2 windows instead of B * S^2 pixels (4x less work, and
+// the 75% zeros of dY are never read).  idx [B, S/2, S/2, C] holds the window slot (0..3, 4 = dead).
+// Block = one image x one group of 32 channels, 160 threads = 32 channels x 5 filter rows.
+//   phase 1 (all threads, batched loads): slot + gradient of every window -> shared memory;
+//   phase 2: thread (c, kh) walks the windows: 5 LDS of the x row under filter row kh + 5 FMAs each.
+template <int S>
+__global__ void __launch_bounds__(160) conv1_wgrad_sparse_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                                 const uint8_t* __restrict__ idx, float* __restrict__ dw,
+                                                                 float* __restrict__ db, int B, int C) {
+  pdl_launch_dependents();
+  constexpr int PS = (S + 1) / 2, XP = S + 4, NW = PS * PS;
+  extern __shared__ __align__(16) float ssm[];
+  float* sx = ssm;                               // [(S + 4)][XP] zero-padded image
+  float* sg = sx + (S + 4) * XP;                 // [NW][32] gradient at the argmax pixel (0 when dead)
+  int* so = reinterpret_cast<int*>(sg + NW * 32); // [NW][32] offset of that pixel's top-left tap in sx
+  const int n = blockIdx.x, cg = blockIdx.y * 32;
+  const int t = threadIdx.x, lane = t & 31, kh = t >> 5;
+  // the image is an input of the step: fetch it before waiting for the kernel that produces dY
+  for (int i = t; i < (S + 4) * XP; i += 160) {
+    const int r = i / XP - 2, cc = i % XP - 2;
+    sx[i] = (r >= 0 && r < S && cc >= 0 && cc < S) ? __ldg(x + (int64_t)n * S * S + r * S + cc) : 0.f;
+  }
+  pdl_wait();
+  // phase 1: 8 windows per trip per thread, slot loads first, then the dependent gradient loads
+  for (int base = 0; base < NW * 32; base += 160 * 8) {
+    int b[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = base + u * 160 + t;
+      b[u] = 4;
+      if (i < NW * 32) b[u] = idx[((int64_t)n * NW + (i >> 5)) * C + cg + (i & 31)];
+    }
+    float g[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = base + u * 160 + t;
+      g[u] = 0.f;
+      if (b[u] < 4) {
+        const int w = i >> 5, ph = w / PS, pw = w % PS;
+        const int uh = 2 * ph + (b[u] >> 1), uw = 2 * pw + (b[u] & 1);
+        g[u] = dy[(((int64_t)n * S + uh) * S + uw) * C + cg + (i & 31)];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = base + u * 160 + t;
+      if (i < NW * 32) {
+        const int w = i >> 5, ph = w / PS, pw = w % PS;
+        const int bb = b[u] < 4 ? b[u] : 0;
+        sg[i] = g[u];
+        so[i] = (2 * ph + (bb >> 1)) * XP + 2 * pw + (bb & 1);
+      }
+    }
+  }
+  __syncthreads();
+  // phase 2
+  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  float bsum = 0.f;
+  const float* xk = sx + kh * XP;
+#pragma unroll 4
+  for (int w = 0; w < NW; ++w) {
+    const float g = sg[w * 32 + lane];
+    const float* xr = xk + so[w * 32 + lane];
+    acc[0] += g * xr[0]; acc[1] += g * xr[1]; acc[2] += g * xr[2]; acc[3] += g * xr[3]; acc[4] += g * xr[4];
+    bsum += g;
+  }
+#pragma unroll
+  for (int kw = 0; kw < 5; ++kw) atomicAdd(dw + (kh * 5 + kw) * C + cg + lane, acc[kw]);
+  if (kh == 0 && db) atomicAdd(db + cg + lane, bsum);
+}
+
 // ------------------------------------------------------------------------------------ pooling
 // bias + ReLU + 2x2 stride-2 SAME max-pool over NHWC raw conv sums (bias may be NULL when the input
 // is already post-ReLU).  Starting the running max at 0 IS the ReLU.
@@ -732,6 +804,24 @@ int ddl_conv1_wgrad(const float* x, const float* dy, float* dw, float* db, int B
   if (S == 28) DDL_LAUNCH(conv1_wgrad_kernel<28>, grid, 192, smem, s, x, dy, dw, db, B, C, strip);
   else if (S == 32) DDL_LAUNCH(conv1_wgrad_kernel<32>, grid, 192, smem, s, x, dy, dw, db, B, C, strip);
   else DDL_REQUIRE(false, "ddl_conv1_wgrad: image size %d not instantiated (28, 32)", S);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+/* conv1 weight / bias gradient from the pooled layout (see conv1_wgrad_sparse_kernel): dy is the un-pooled gradient
+ * [B,S,S,C] (only its argmax pixels are read), idx [B,S/2,S/2,C] the argmax slots.  x is read before
+ * griddepcontrol.wait: it must not be produced by the kernel launched just before. */
+int ddl_conv1_wgrad_sparse(const float* x, const float* dy, const uint8_t* idx, float* dw, float* db, int B, int S, int C,
+                           cudaStream_t s) {
+  DDL_REQUIRE(C % 32 == 0 && S == 28, "ddl_conv1_wgrad_sparse: C %% 32 == 0 and S == 28 (got C=%d S=%d)", C, S);
+  constexpr int S28 = 28, PS = 14;
+  const size_t smem = ((size_t)(S28 + 4) * (S28 + 4) + (size_t)PS * PS * 32 * 2) * sizeof(float);
+  static bool attr_done = false;
+  if (!attr_done) {
+    DDL_CHECK_CUDA(cudaFuncSetAttribute(conv1_wgrad_sparse_kernel<28>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_done = true;
+  }
+  DDL_LAUNCH(conv1_wgrad_sparse_kernel<28>, dim3(B, C / 32), 160, smem, s, x, dy, idx, dw, db, B, C);
   DDL_LAUNCH_CHECK();
   return 0;
 }

@@ -60,6 +60,7 @@ struct DdlEngine {
   DdlTcPlan* dg_conv[3] = {};
   int dg_split[3] = {1, 1, 1};
   bool dg_unpool[3] = {false, false, false};   // dgrad plan's epilogue is the pool + ReLU backward of the layer below
+  bool w1_fused = false;                       // ... and dg_conv[0] also emits conv1's weight / bias gradient
   DdlTcPlan* wg_fc[2] = {};
   DdlTcPlan* dg_fc[2] = {};        // dg_fc[0]: fc1 -> dp4 (cnn only), dg_fc[1]: fc2 -> dh1
   std::vector<void*> allocs;
@@ -247,6 +248,23 @@ int build_bwd(DdlEngine* e) {
                                                    l - 1 >= 1 ? e->G(v - 1) : nullptr, B, S, S, US, US, cout, cin, 5, nt, ks);
       if (!e->dg_conv[l - 1]) return -1;
       e->dg_unpool[l - 1] = true;
+      // conv2's dgrad also produces conv1's weight and bias gradient (conv1 has one input channel): no un-pooled
+      // gradient tensor, no conv1 wgrad kernel at the tail of the step.  x is re-pointed before every run.
+      // Measured (tools/w1_perf.py): the fused pass costs the dgrad kernel ~25 us (128 epilogue threads walk 119 pixels x
+      // 7 taps each) against 18 us for the separate kernel it replaces - neutral in the step, so it is opt-in
+      // (DDL_W1_FUSE=1) and the sparse stand-alone kernel below is the default.
+      static const bool no_w1 = getenv("DDL_W1_FUSE") == nullptr;
+      if (l == 1 && e->C[0] == 1 && !no_w1) {
+        DdlTcPlan* alt = ddl_tc_plan_dgrad_unpool(e->dfull[l], e->P(v), e->idx[0], e->dfull[0], e->G(1), B, S, S, US, US, cout,
+                                                  cin, 5, nt, ks);
+        if (alt && ddl_tc_plan_unpool_w1grad(alt, e->pooled[0], e->G(0), 5, 0) == 0) {
+          ddl_tc_plan_destroy(e->dg_conv[0]);
+          e->dg_conv[0] = alt;
+          e->w1_fused = true;
+        } else if (alt) {
+          ddl_tc_plan_destroy(alt);
+        }
+      }
       continue;
     }
     pick_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), true, &nt, &ks);
@@ -457,6 +475,7 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
       if (fork(wl)) return -1;
       if (ddl_tc_plan_run(e->wg_conv[l - 1], wl)) return -1;
       if (l == 3) DDL_CHECK_CUDA(cudaEventRecord(e->ev_w0, w));
+      if (l == 1 && e->w1_fused && ddl_tc_plan_set_x1(e->dg_conv[0], x)) return -1;
       if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
       if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
     }
@@ -474,7 +493,16 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
   }
   if (!unpool && ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull[0], nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
-  if (ddl_conv1_wgrad(x, e->dfull[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
+  if (!(unpool && e->w1_fused)) {
+    // the sparse (argmax-pixels-only) kernel does a quarter of the arithmetic but is slower inside the step (371k vs
+    // 385k samples/s: one block per image, two dependent load levels) - opt-in with DDL_W1_SPARSE=1
+    static const bool sparse_w1 = getenv("DDL_W1_SPARSE") != nullptr;
+    if (sparse_w1 && e->S[0] == 28 && e->C[1] % 32 == 0) {
+      if (ddl_conv1_wgrad_sparse(x, e->dfull[0], e->idx[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
+    } else if (ddl_conv1_wgrad(x, e->dfull[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) {
+      return -1;
+    }
+  }
   DDL_CHECK_CUDA(cudaEventRecord(e->ev_join, w));
   DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join, 0));
   if (!one_wstream) {

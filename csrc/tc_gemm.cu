@@ -34,6 +34,7 @@ constexpr int kKB = 32;            // fp32 elements per K-block = one 128-byte s
 constexpr int kUmmaK = 8;          // tf32: 32 bytes of K per instruction
 constexpr int kThreadsTc = 192;    // 6 warps
 constexpr int kMaxStages = 8;
+constexpr int kW1Pitch = 132;      // bytes per channel row of the argmax-slot stash of the fused first-layer wgrad
 
 struct ActParams {
   // pixel space of the activation operand and of the output
@@ -70,6 +71,13 @@ struct ActParams {
   uint8_t* pool_idx;               // argmax slots: written by EPI_POOL (nullable), read by EPI_UNPOOL
   int UH, UW;                      // EPI_UNPOOL: un-pooled plane (H = ceil(UH/2), W = ceil(UW/2))
   float* dbias;                    // EPI_UNPOOL: += column sums of the routed gradient (nullable)
+  // EPI_UNPOOL + first-layer weight gradient (the layer below has ONE input channel, conv1): the epilogue also
+  // accumulates dW1[tap][c] += g * x1[pixel of the argmax slot + tap offset] - only the argmax slots are non-zero, so
+  // this is 1/4 of the separate kernel's work and needs no second pass over the un-pooled gradient
+  const float* x1;                 // [N, UH, UW] single-channel input of the layer below (nullable = off)
+  float* dw1;                      // [k1*k1][nout]
+  int k1;                          // its filter size
+  int aux_off;                     // byte offset of the x patch + slot stash in shared memory
 };
 
 struct WgradParams {
@@ -129,7 +137,9 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const bool ptrace = (p.debug & 16) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0;
   if (ptrace && threadIdx.x == 0) p.trace[0] = ddl_globaltimer();
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  // 1024-byte alignment by pointer arithmetic on the __shared__ array (an integer round trip would turn every later
+  // access into a generic LD.E / ST.E instead of LDS / STS)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int a_bytes = kTileM * 128;
   const int b_bytes = p.ntile * 128;
   const int stage_bytes = a_bytes + b_bytes;
@@ -172,6 +182,22 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   // everything above overlapped the previous kernel; its data (the activation operand) is needed from here.  The
   // weight operand is not produced by the preceding kernels (see ddl::no_pdl_once), so the B producer (warp 3) starts
   // filling the pipeline right away and only joins the wait before its epilogue duty.
+  const bool w1grad = (p.flags & EPI_UNPOOL) && p.x1 != nullptr;
+  // zero-padded patch of the single-channel image under this tile's un-pooled pixels (+ filter halo); x1 is an input
+  // of the step, not an output of the previous kernel, so warps 2, 4, 5 fetch it before the wait
+  const int k1h = p.k1 / 2;
+  const int xpw = 2 * p.bw + 2 * k1h, xph = 2 * p.bh + 2 * k1h;
+  float* xs = reinterpret_cast<float*>(smem + p.aux_off);
+  uint8_t* sidx = reinterpret_cast<uint8_t*>(xs) + (w1grad ? ((p.bn * xph * xpw * 4 + 15) & ~15) : 0);
+  if (w1grad && warp >= 2 && warp != 3 && !(p.debug & 512)) {
+    const int tl = (warp == 2 ? 0 : warp - 3) * 32 + lane;          // 0..95
+    const int total = p.bn * xph * xpw;
+    for (int i = tl; i < total; i += 96) {
+      const int xw = i % xpw, xh = (i / xpw) % xph, xn = i / (xpw * xph);
+      const int gw = 2 * w0 + xw - k1h, gh = 2 * h0 + xh - k1h, gn = n0 + xn;
+      xs[i] = (gn < p.N && gh >= 0 && gh < p.UH && gw >= 0 && gw < p.UW) ? __ldg(p.x1 + ((int64_t)gn * p.UH + gh) * p.UW + gw) : 0.f;
+    }
+  }
   const bool early_b = !p.pull;
   if (!(early_b && warp == 3)) pdl_wait();
   if (ptrace && threadIdx.x == 0) p.trace[2] = ddl_globaltimer();
@@ -444,6 +470,10 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
             bi[u] = make_uchar4(4, 4, 4, 4);
             if (ok[u]) {
               bi[u] = *reinterpret_cast<const uchar4*>(pidx + (((int64_t)gn * p.H + gh[u]) * p.W + gw[u]) * p.nout + colv[u]);
+              if (w1grad) {                      // slot stash [channel][kW1Pitch]: a thread of the wgrad pass reads 4 pixels per LDS
+                uint8_t* sd = sidx + (4 * c4) * kW1Pitch + r;
+                sd[0] = bi[u].x; sd[kW1Pitch] = bi[u].y; sd[2 * kW1Pitch] = bi[u].z; sd[3 * kW1Pitch] = bi[u].w;
+              }
               const float* sr = S + r * sp + c4;
 #pragma unroll
               for (int q4 = 0; q4 < 4; ++q4) g[u][q4] = sr[q4 * cq4];
@@ -457,7 +487,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const int uh = 2 * gh[u] + (k >> 1), uw = 2 * gw[u] + (k & 1);
-              if (uh < p.UH && uw < p.UW)
+              if (pout && uh < p.UH && uw < p.UW)
                 *reinterpret_cast<float4*>(pout + ((obase[u] + uh) * p.UW + uw) * p.nout + colv[u]) =
                     make_float4(b4[0] == k ? g[u][0] : 0.f, b4[1] == k ? g[u][1] : 0.f, b4[2] == k ? g[u][2] : 0.f,
                                 b4[3] == k ? g[u][3] : 0.f);
@@ -487,6 +517,56 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
 #pragma unroll
             for (int q4 = 0; q4 < 4; ++q4)
               if (dbsum[q4] != 0.f && col + q4 < p.nout) atomicAdd(p.dbias + col + q4, dbsum[q4]);
+          }
+        }
+        if (w1grad) {
+          // thread <-> (channel c, tap group): walks every pooled pixel of the tile, one LDS of the gradient and of its
+          // argmax slot, then <= kW1Taps FMAs against the image patch
+          constexpr int kW1Taps = 13;
+          named_bar_sync(1, 128);                      // slot stash complete (S was complete before)
+          const int c = te % cw, tg = te / cw, ngroups = 128 / cw;
+          const int taps1 = p.k1 * p.k1;
+          const int tpg = (taps1 + ngroups - 1) / ngroups;       // taps per group (<= kW1Taps: cw <= 64)
+          const int t0 = tg * tpg;
+          float acc[kW1Taps];
+#pragma unroll
+          for (int j = 0; j < kW1Taps; ++j) acc[j] = 0.f;
+          const int cp = spos(c, cw);
+          int off[kW1Taps];                          // patch offset of each of my taps (no divisions in the pixel loop)
+#pragma unroll
+          for (int j = 0; j < kW1Taps; ++j) {
+            const int tap = t0 + j;
+            off[j] = (j < tpg && tap < taps1) ? (tap / p.k1) * xpw + tap % p.k1 : -1;
+          }
+          // patch offset of every pooled pixel of the tile (-1: outside the tensor), computed once by 128 threads
+          int* roff = reinterpret_cast<int*>(sidx + cw * kW1Pitch);
+          {
+            const int rw = te % p.bw, rh = (te / p.bw) % p.bh, rn = te / (p.bw * p.bh);
+            const bool in = te < R && n0 + rn < p.N && h0 + rh < p.H && w0 + rw < p.W;
+            roff[te] = in ? (rn * xph + 2 * rh) * xpw + 2 * rw : -1;
+          }
+          named_bar_sync(1, 128);
+          // 4 pooled pixels per trip: one LDS.32 of argmax slots, one LDS.128 of patch offsets, then 4 x taps independent
+          // LDS + FMA (dead / outside pixels contribute g = 0 at slot 0)
+          for (int r4 = 0; r4 < ((p.debug & 256) ? 0 : R); r4 += 4) {
+            const uint32_t b4w = *reinterpret_cast<const uint32_t*>(sidx + c * kW1Pitch + r4);
+            const int4 ro = *reinterpret_cast<const int4*>(roff + r4);
+            const int rov[4] = {ro.x, ro.y, ro.z, ro.w};
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const int b = (int)((b4w >> (8 * q4)) & 0xffu);
+              const bool live = b < 4 && rov[q4] >= 0 && r4 + q4 < R;
+              const float g = live ? S[(r4 + q4) * sp + cp] : 0.f;
+              const float* xr = xs + (live ? rov[q4] + (b >> 1) * xpw + (b & 1) : 0);
+#pragma unroll
+              for (int j = 0; j < kW1Taps; ++j)
+                if (off[j] >= 0) acc[j] += g * xr[off[j]];
+            }
+          }
+          if (colbase + c < p.nout && !(p.debug & 128)) {
+#pragma unroll
+            for (int j = 0; j < kW1Taps; ++j)
+              if (off[j] >= 0 && acc[j] != 0.f) atomicAdd(p.dw1 + (int64_t)(t0 + j) * p.nout + colbase + c, acc[j]);
           }
         }
       }
@@ -611,7 +691,9 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
                 const WgradParams p) {
   pdl_launch_dependents();
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  // 1024-byte alignment by pointer arithmetic on the __shared__ array (an integer round trip would turn every later
+  // access into a generic LD.E / ST.E instead of LDS / STS)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int R = p.bw * p.bh * p.bn;
   const int box_bytes = R * 128;
   const int b_boxes = p.ntile / 32;                       // atoms per tap
@@ -915,6 +997,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   p.pool_idx = po ? po->idx : nullptr;
   p.dbias = po ? po->dbias : nullptr;
   p.UH = po ? po->UH : 0; p.UW = po ? po->UW : 0;
+  p.x1 = nullptr; p.dw1 = nullptr; p.k1 = 0; p.aux_off = 0;
   p.pull = (w_store_dst != nullptr && !dgrad && w_store_dst != w) ? 1 : 0;
   p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
   p.trace = nullptr;
@@ -1009,6 +1092,43 @@ DdlTcPlan* ddl_tc_plan_dgrad_unpool(const float* dy, const float* w, const uint8
   if ((UH + 1) / 2 != H || (UW + 1) / 2 != W) { ddl::set_error("ddl_tc_plan_dgrad_unpool: plane %dx%d does not pool to %dx%d", UH, UW, H, W); return nullptr; }
   return plan_act_impl(1, dy, w, nullptr, N, H, W, cout, cin, ksize, ntile, cluster, 0, nullptr, nullptr, 1.f, nullptr, 0,
                        1.f, nullptr, nullptr, &po);
+}
+
+/* Adds the weight gradient of a ONE-input-channel layer below (conv1) to a dgrad_unpool plan: dw1[k1*k1][cin] +=
+ * sum over the routed gradient's non-zero (argmax) pixels of g * x1[pixel + tap offset]; x1 is [N, UH, UW].
+ * store_dfull = 0 additionally drops the un-pooled gradient itself (nothing else consumes it then).
+ * ddl_tc_plan_set_x1 re-points x1 before a run (the engine alternates input buffers). */
+int ddl_tc_plan_unpool_w1grad(DdlTcPlan* pl, const float* x1, float* dw1, int k1, int store_dfull) {
+  DDL_REQUIRE(pl && pl->kind == 0 && (pl->act.flags & EPI_UNPOOL), "ddl_tc_plan_unpool_w1grad: not a dgrad_unpool plan");
+  ActParams& p = pl->act;
+  const int cw = p.ntile / p.cluster;
+  DDL_REQUIRE(cw <= 64 && 128 % cw == 0 && k1 >= 1 && (k1 & 1) && k1 * k1 <= 13 * (128 / cw),
+              "ddl_tc_plan_unpool_w1grad: N tile / cluster = %d and filter %d not supported", cw, k1);
+  DDL_REQUIRE(x1 != nullptr && dw1 != nullptr, "ddl_tc_plan_unpool_w1grad: null pointer");
+  p.x1 = x1; p.dw1 = dw1; p.k1 = k1;
+  if (!store_dfull) p.pool_out = nullptr;
+  const size_t patch = (size_t)p.bn * (2 * p.bh + 2 * (k1 / 2)) * (2 * p.bw + 2 * (k1 / 2)) * sizeof(float);
+  const size_t stage_bytes = (size_t)kTileM * 128 + (size_t)p.ntile * 128;
+  const size_t epi_bytes = (p.cluster > 1 ? (size_t)p.ntile * 512 : 0) + (size_t)128 * (cw + 1) * sizeof(float);
+  for (;;) {
+    size_t bars_off = (size_t)p.stages * stage_bytes;
+    if (epi_bytes > bars_off) bars_off = (epi_bytes + 15) & ~(size_t)15;
+    p.bars_off = (int)bars_off;
+    const size_t aux_off = (bars_off + sizeof(PipeBars) + 15) & ~(size_t)15;
+    p.aux_off = (int)aux_off;
+    pl->smem = aux_off + ((patch + 15) & ~(size_t)15) + (size_t)cw * kW1Pitch + 128 * sizeof(int) + 1024;   // patch, slots, offsets
+    // keep two CTAs per SM resident (the patch must not push a ~100 KB pipeline over half an SM): drop a stage instead
+    if (pl->smem <= 110 * 1024 || p.stages <= 3) break;
+    --p.stages;
+  }
+  DDL_REQUIRE(pl->smem <= 227 * 1024, "ddl_tc_plan_unpool_w1grad: tile does not fit shared memory");
+  return 0;
+}
+
+int ddl_tc_plan_set_x1(DdlTcPlan* pl, const float* x1) {
+  DDL_REQUIRE(pl && pl->kind == 0 && pl->act.x1 != nullptr && x1 != nullptr, "ddl_tc_plan_set_x1: plan has no fused first-layer wgrad");
+  pl->act.x1 = x1;
+  return 0;
 }
 
 DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,

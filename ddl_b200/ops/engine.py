@@ -71,9 +71,11 @@ class NativeBackend:
         advanced (``advance_state``) by the caller."""
         native.check(self.L.ddl_engine_train_step(self.h, native.ptr(x), native.ptr(y), native.stream_ptr()),
                      "ddl_engine_train_step")
-        # engine kernels per step: 20 with the pools fused into the conv / dgrad epilogues, 26 with DDL_NO_POOL_FUSE
+        # engine kernels per step: 19 (pools fused into the conv / dgrad epilogues, one fc3 kernel; 18 with conv1's wgrad
+        # inside conv2's dgrad, DDL_W1_FUSE=1), 26 with DDL_NO_POOL_FUSE
         # (+ the overlapped push bucket)
-        native.count((26 if os.environ.get("DDL_NO_POOL_FUSE") else 20) + getattr(self, "overlap_launches", 0))
+        n = 26 if os.environ.get("DDL_NO_POOL_FUSE") else 19 + bool(os.environ.get("DDL_FC3_SPLIT")) - bool(os.environ.get("DDL_W1_FUSE"))
+        native.count(n + getattr(self, "overlap_launches", 0))
 
     def advance_state(self, advance_opt: bool = True) -> None:
         c = self.cfg

@@ -99,6 +99,7 @@ def lib() -> C.CDLL:
         "ddl_optimizer_step": ([i32, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, vp, vp], i32),
         "ddl_conv1_relu_pool": ([vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
         "ddl_conv1_wgrad": ([vp, vp, vp, vp, i32, i32, i32, vp], i32),
+        "ddl_conv1_wgrad_sparse": ([vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
         "ddl_maxpool_fwd": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], i32),
         "ddl_maxpool_bwd": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], i32),
         "ddl_colsum": ([vp, vp, i32, i32, vp], i32),
@@ -112,6 +113,8 @@ def lib() -> C.CDLL:
         "ddl_tc_plan_wgrad": ([vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_tc_plan_conv_pool": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_tc_plan_dgrad_unpool": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32], vp),
+        "ddl_tc_plan_unpool_w1grad": ([vp, vp, vp, i32, i32], i32),
+        "ddl_tc_plan_set_x1": ([vp, vp], i32),
         "ddl_tc_plan_run": ([vp, vp], i32),
         "ddl_tc_plan_destroy": ([vp], None),
         "ddl_tc_plan_info": ([vp, C.POINTER(C.c_int)], i32),

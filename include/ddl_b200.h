@@ -55,6 +55,10 @@ int ddl_conv1_relu_pool(const float* x, const float* w, const float* bias, float
                         int B, int S, int C, cudaStream_t s);
 int ddl_conv1_wgrad(const float* x, const float* dy, float* dw, float* db, int B, int S, int C,
                     cudaStream_t s);
+/* the same gradients from the POOLED layout: after pool + ReLU backward only the argmax pixel of each 2x2 window is
+ * non-zero, so the sum runs over the windows (idx [B,S/2,S/2,C], slots 0..3, 4 = dead) - a quarter of the work */
+int ddl_conv1_wgrad_sparse(const float* x, const float* dy, const uint8_t* idx, float* dw, float* db, int B, int S, int C,
+                           cudaStream_t s);
 /* (bias +) ReLU + tf.nn.max_pool2d 2x2/2 SAME on NHWC conv sums and its gradient (model.py:31,42,53,64);
  * the backward also accumulates the bias gradient of the producing conv into db (may be NULL). */
 int ddl_maxpool_fwd(const float* a, const float* bias, float* y, uint8_t* idx, int B, int H, int W, int C,
@@ -126,6 +130,12 @@ DdlTcPlan* ddl_tc_plan_conv_pool(const float* act, const float* w, const float* 
 DdlTcPlan* ddl_tc_plan_dgrad_unpool(const float* dy, const float* w, const uint8_t* idx, float* dfull, float* dbias,
                                     int N, int H, int W, int UH, int UW, int cout, int cin, int ksize, int ntile,
                                     int cluster);
+/* Fold the weight gradient of the ONE-input-channel layer below (conv1, model.py:24-31) into a dgrad_unpool plan:
+ * dw1[k1*k1][cin] += sum over the argmax pixels of the routed gradient of g * x1[pixel + tap offset], x1 [N, UH, UW].
+ * Only 1/4 of the un-pooled gradient is non-zero, so this replaces a full pass over it.  store_dfull = 0 also drops
+ * the un-pooled gradient tensor itself.  ddl_tc_plan_set_x1 re-points x1 (alternating input buffers). */
+int ddl_tc_plan_unpool_w1grad(DdlTcPlan* pl, const float* x1, float* dw1, int k1, int store_dfull);
+int ddl_tc_plan_set_x1(DdlTcPlan* pl, const float* x1);
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);
 void ddl_tc_plan_destroy(DdlTcPlan* pl);
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8);

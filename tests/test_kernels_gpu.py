@@ -76,6 +76,21 @@ def test_conv1_relu_pool_and_wgrad():
     assert rel_err(dw, w.grad) < 1e-4 and rel_err(db, b.grad) < 1e-4
 
 
+@pytest.mark.parametrize("B,C", [(100, 32), (7, 64)])
+def test_conv1_wgrad_sparse_matches_dense(B, C):
+    """conv1 gradients from the argmax pixels only, against the dense kernel on the same routed gradient."""
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(14)
+    x = torch.randn(B, 28, 28, device=dev())
+    below = torch.randn(B, 28, 28, C, device=dev())
+    _, idx = K.bias_relu_maxpool(below)
+    dp = torch.randn(B, 14, 14, C, device=dev())
+    dy, _ = K.maxpool_relu_bwd(dp, idx, 28, 28)
+    want_dw, want_db = K.conv1_wgrad(x, dy)
+    dw, db = K.conv1_wgrad_sparse(x, dy, idx)
+    assert rel_err(dw, want_dw) < 1e-4 and rel_err(db, want_db) < 1e-4
+
+
 @pytest.mark.parametrize("H,C", [(14, 64), (7, 128), (4, 256)])
 def test_bias_relu_maxpool_fwd_bwd(H, C):
     from ddl_b200.ops import functional as K
@@ -166,6 +181,34 @@ def test_tc_conv_dgrad_unpool_fused(H, UH, Cin, Cout, B, ntile, cluster):
     assert rel_err(got, xb.grad.float()) < TF32_TOL
     got2, none = K.conv5x5_dgrad_unpool(dy, w, idx, UH, UH, ntile=ntile, cluster=cluster, want_db=False)
     assert none is None and torch.equal(got2, got)
+
+
+@pytest.mark.parametrize("B,Cin,ntile,cluster,store", [(100, 32, 32, 1, True), (100, 32, 32, 1, False), (37, 64, 64, 1, True),
+                                                       (100, 32, 32, 2, True), (50, 64, 32, 1, True)])
+def test_tc_dgrad_unpool_with_first_layer_wgrad(B, Cin, ntile, cluster, store):
+    """conv2 dgrad + pool1 backward + conv1's weight AND bias gradient in one kernel, against conv1_wgrad."""
+    from ddl_b200.ops import functional as K
+    torch.manual_seed(13)
+    H, UH, Cout = 14, 28, 64
+    dy = torch.randn(B, H, H, Cout, device=dev())
+    w = torch.randn(5, 5, Cin, Cout, device=dev()) * 0.05
+    x1 = torch.randn(B, UH, UH, device=dev())
+    below = torch.randn(B, UH, UH, Cin, device=dev())
+    _, idx = K.bias_relu_maxpool(below)
+    want, want_db = K.conv5x5_dgrad_unpool(dy, w, idx, UH, UH, ntile=ntile, cluster=cluster)
+    want_dw1, want_db1 = K.conv1_wgrad(x1, want)
+    got, db, dw1 = K.conv5x5_dgrad_unpool(dy, w, idx, UH, UH, ntile=ntile, cluster=cluster, x1=x1, store_dfull=store)
+    assert (got is None) == (not store)
+    if store:
+        assert torch.equal(got, want)
+    assert rel_err(db, want_db) < 1e-3 and rel_err(db, want_db1) < 1e-3
+    assert dw1.shape == want_dw1.shape and rel_err(dw1, want_dw1) < 1e-3
+    # and against torch: dW1 = conv weight gradient of a 1-channel conv
+    xr = x1.double().unsqueeze(1).requires_grad_(False)
+    wt = torch.zeros(Cin, 1, 5, 5, device=dev(), dtype=torch.double, requires_grad=True)
+    y = F.conv2d(xr, wt, padding=2)
+    y.backward(want.double().permute(0, 3, 1, 2))
+    assert rel_err(dw1.squeeze(2).permute(2, 0, 1), wt.grad.squeeze(1).float()) < 1e-3
 
 
 @pytest.mark.parametrize("H,Cin,Cout", [(14, 32, 64), (7, 64, 128), (4, 128, 256)])
