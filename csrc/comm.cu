@@ -30,7 +30,7 @@ namespace {
 constexpr int kCommThreads = 512;
 
 // perf experiments: globaltimer stamps of block 0 / thread 0 of the sync kernel (tools/sync_phase.py)
-__device__ int g_cstamps_on = 0;
+static int g_cstamps_host = 0;                // passed as a kernel argument: no device-side flag load on the hot path
 __device__ unsigned long long g_cstamps[16];
 #define DDL_CSTAMP(i) do { if (cst) g_cstamps[i] = ddl_globaltimer(); } while (0)
 
@@ -106,10 +106,10 @@ DDL_DEVICE float4 opt_apply(float4 pv, float4 gv, float* m, float* v, int64_t i,
 // trip), U = 4 for bandwidth-bound large ones.
 template <int KIND, int U>
 __global__ void __launch_bounds__(kCommThreads)
-sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a) {
+sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int stamps_on) {
   pdl_enter();
   __shared__ uint32_t s_last;
-  const bool cst = g_cstamps_on && blockIdx.x == 0 && threadIdx.x == 0 && a.bucket == 0;
+  const bool cst = stamps_on && blockIdx.x == 0 && threadIdx.x == 0 && a.bucket == 0;
   DDL_CSTAMP(0);
   const uint32_t t = a.st->t;                       // same on every rank: all ranks advance together
   const uint32_t nb = a.nbuckets > 1 ? (uint32_t)a.nbuckets : 1u;
@@ -379,7 +379,7 @@ extern "C" {
 
 /* perf experiments: enable / read the globaltimer stamps of the sync kernel's block 0 (bucket 0) */
 int ddl_comm_stamps(int on, unsigned long long* out, int n) {
-  DDL_CHECK_CUDA(cudaMemcpyToSymbol(g_cstamps_on, &on, sizeof(int)));
+  g_cstamps_host = on;
   if (out && n > 0) DDL_CHECK_CUDA(cudaMemcpyFromSymbol(out, g_cstamps, sizeof(unsigned long long) * (n > 16 ? 16 : n)));
   return 0;
 }
@@ -430,13 +430,13 @@ int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, 
   static const int force_u = getenv("DDL_COMM_UNROLL") ? atoi(getenv("DDL_COMM_UNROLL")) : 0;
   const bool wide = force_u ? force_u > 1 : (c->mc_grads == nullptr && elems / 4 >= (int64_t)grid * kCommThreads * 16);
   if (wide) {
-    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 4>), grid, kCommThreads, 0, s, *c, *a);
-    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 4>), grid, kCommThreads, 0, s, *c, *a);
-    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 4>), grid, kCommThreads, 0, s, *c, *a);
+    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
+    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
+    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
   } else {
-    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 1>), grid, kCommThreads, 0, s, *c, *a);
-    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 1>), grid, kCommThreads, 0, s, *c, *a);
-    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 1>), grid, kCommThreads, 0, s, *c, *a);
+    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
+    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
+    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
   }
   DDL_LAUNCH_CHECK();
   return 0;

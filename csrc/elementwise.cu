@@ -517,7 +517,7 @@ __global__ void fc3_bwd_kernel(const float* __restrict__ h, const float* __restr
 constexpr int kFc3Cluster = 8;
 constexpr int kFc3Threads = 1024;
 // perf experiments: globaltimer stamps of CTA 0 / thread 0 (tools/fc3_phase.py); off unless ddl_debug_stamps(1)
-__device__ int g_stamps_on = 0;
+static int g_stamps_host = 0;                 // passed as a kernel argument: no device-side flag load on the hot path
 __device__ unsigned long long g_stamps[32];
 #define DDL_STAMP(i) do { if (stamps && threadIdx.x == 0) g_stamps[i] = ddl_globaltimer(); } while (0)
 
@@ -527,7 +527,8 @@ __global__ void __launch_bounds__(kFc3Threads) fc3_cluster_kernel(const float* _
                                                                   float* __restrict__ dw, float* __restrict__ db,
                                                                   float* __restrict__ dh, float* __restrict__ dbh,
                                                                   DdlStepState* st, int B, int K, int NC, int KS, float scale,
-                                                                  uint32_t stream_off, uint32_t thresh24, float inv_keep) {
+                                                                  uint32_t stream_off, uint32_t thresh24, float inv_keep,
+                                                                  int stamps_on) {
   pdl_launch_dependents();
   cluster_arrive_release();                // "I am running": peers may store into my shared memory after the matching wait
   extern __shared__ __align__(16) float sm[];
@@ -537,7 +538,7 @@ __global__ void __launch_bounds__(kFc3Threads) fc3_cluster_kernel(const float* _
   float* scol = shs + B * (KS + 1);        // [KS]        column sums of dh
   const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
   const int crank = (int)cluster_ctarank();
-  const bool stamps = g_stamps_on && crank == 0;
+  const bool stamps = stamps_on && crank == 0;
   DDL_STAMP(0);
   const int k0 = crank * KS;
   // ---- phase 0: loads that do not depend on the previous kernel
@@ -919,17 +920,17 @@ int ddl_fc3_fused_st(const float* h, const float* w, const float* bias, const in
   const float inv_keep = keep_prob >= 1.f ? 1.f : 1.f / keep_prob;
   if (NC <= 12)
     DDL_CHECK_CUDA(ddl::launch(fc3_cluster_kernel<12>, dim3(1, 1, kFc3Cluster), dim3(kFc3Threads), smem, s, (unsigned)kFc3Cluster,
-                               h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, KS, scale, stream_off, thresh, inv_keep));
+                               h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, KS, scale, stream_off, thresh, inv_keep, g_stamps_host));
   else
     DDL_CHECK_CUDA(ddl::launch(fc3_cluster_kernel<16>, dim3(1, 1, kFc3Cluster), dim3(kFc3Threads), smem, s, (unsigned)kFc3Cluster,
-                               h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, KS, scale, stream_off, thresh, inv_keep));
+                               h, w, bias, labels, dw, db, dh, dbh, st, B, K, NC, KS, scale, stream_off, thresh, inv_keep, g_stamps_host));
   DDL_LAUNCH_CHECK();
   return 0;
 }
 
 /* perf experiments: enable / read the globaltimer stamps of fc3_cluster_kernel */
 int ddl_debug_stamps(int on, unsigned long long* out, int n) {
-  DDL_CHECK_CUDA(cudaMemcpyToSymbol(g_stamps_on, &on, sizeof(int)));
+  g_stamps_host = on;
   if (out && n > 0) DDL_CHECK_CUDA(cudaMemcpyFromSymbol(out, g_stamps, sizeof(unsigned long long) * (n > 32 ? 32 : n)));
   return 0;
 }

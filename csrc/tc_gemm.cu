@@ -608,11 +608,24 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
 #pragma unroll
           for (int j = 0; j < 16; ++j) v[j] = 0.f;
         }
-        for (int r = 0; r < p.cluster - 1; ++r) {
+        // four peers per batch, every load of a batch issued before the first add: one L2 round trip per batch
+        // instead of one per peer (the rolled loop cost (cluster - 1) dependent latencies per chunk, tools/tc_phase.py)
+        for (int r0 = 0; r0 < p.cluster - 1; r0 += 4) {
+          float4 t[4][4];
 #pragma unroll
-          for (int j = 0; j < 16; j += 4) {
-            const float4 t = __ldcg(parts + ((size_t)r * (p.ntile / 4) + (c0 + j) / 4) * 128);
-            v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
+          for (int k = 0; k < 4; ++k) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              t[k][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (r0 + k < p.cluster - 1) t[k][j] = __ldcg(parts + ((size_t)(r0 + k) * (p.ntile / 4) + c0 / 4 + j) * 128);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              v[4 * j] += t[k][j].x; v[4 * j + 1] += t[k][j].y; v[4 * j + 2] += t[k][j].z; v[4 * j + 3] += t[k][j].w;
+            }
           }
         }
       }

@@ -93,6 +93,21 @@ def launch(variant_dir: str, num_ps: int, num_workers: int, extra: List[str], tr
     return rc
 
 
+def launch_with_retry(variant_dir: str, num_ps: int, num_workers: int, extra: List[str], transport: str = "auto",
+                      timeout: float = 0.0, attempts: int = 2) -> int:
+    """``launch``; a job that dies within its first seconds (rendezvous port taken between ``free_port`` and the
+    bind, a rank killed while importing) is started once more on a fresh port.  Later failures are returned as is."""
+    rc = 0
+    for k in range(max(1, attempts)):
+        t0 = time.time()
+        rc = launch(variant_dir, num_ps, num_workers, extra, transport, timeout)
+        if rc == 0 or rc == 124 or time.time() - t0 > 20.0 or k + 1 == attempts:
+            return rc
+        print("[launch] job failed after %.1f s (rc %d) - retrying on a new port" % (time.time() - t0, rc),
+              file=sys.stderr, flush=True)
+    return rc
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(description="run.sh <num_ps> <num_workers> [role flags...]")
     ap.add_argument("--variant-dir", default=".")
@@ -101,7 +116,8 @@ def main(argv=None) -> int:
     ap.add_argument("num_ps", type=int)
     ap.add_argument("num_workers", type=int)
     ns, extra = ap.parse_known_args(argv)
-    return launch(os.path.abspath(ns.variant_dir), ns.num_ps, ns.num_workers, extra, ns.transport, ns.timeout)
+    return launch_with_retry(os.path.abspath(ns.variant_dir), ns.num_ps, ns.num_workers, extra, ns.transport, ns.timeout,
+                             attempts=int(os.environ.get("DDL_LAUNCH_ATTEMPTS", "2")))
 
 
 if __name__ == "__main__":
