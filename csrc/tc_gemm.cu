@@ -47,6 +47,8 @@ struct ActParams {
   int ksplit;                      // gridDim.z
   int nout, ntile;                 // output channels, UMMA N
   int stages;
+  int kps;                         // K blocks (32 reduction channels each) per pipeline stage: 1 or 2.  Two halve the
+                                   // barrier round trips (wait + commit ~175 of ~600 cycles per K block, tc_issue_latency.md)
   int b_mn_major;                  // 1: weights [tap][cred][nout] (fprop), 0: [tap][nout][cred] (dgrad)
   int flags;
   int cluster;                     // > 1: the ksplit CTAs of a tile form a thread-block cluster; ranks 1.. park their
@@ -142,7 +144,8 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int a_bytes = kTileM * 128;
   const int b_bytes = p.ntile * 128;
-  const int stage_bytes = a_bytes + b_bytes;
+  const int stage_bytes = p.kps * (a_bytes + b_bytes);    // [A x kps | B x kps]
+  const int sb_off = p.kps * a_bytes;                     // first B block of a stage
   PipeBars* bars = (PipeBars*)(smem + (size_t)p.bars_off);
 
   const int warp = warp_id_uniform(), lane = threadIdx.x & 31;
@@ -153,7 +156,8 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const int per = (p.kiters + p.ksplit - 1) / p.ksplit;
   const int k_begin = blockIdx.z * per;
   const int k_end = min(p.kiters, k_begin + per);
-  const int niter = max(0, k_end - k_begin);
+  const int niter = max(0, k_end - k_begin);              // K blocks of this CTA
+  const int nst = (niter + p.kps - 1) / p.kps;            // pipeline stage fills (kps K blocks each, the last may be short)
   const uint32_t ncols = tmem_cols_for(p.ntile);
   const bool creduce = p.cluster > 1;
   const bool staged = (p.flags & (EPI_POOL | EPI_UNPOOL)) != 0;
@@ -233,19 +237,23 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     int s = 0;
     uint32_t ph = 0;
     int tap = k_begin / p.cblocks, cb = k_begin % p.cblocks;
-    for (int i = 0; i < niter; ++i) {
+    for (int i = 0; i < nst; ++i) {
+      const int cnt = min(p.kps, niter - i * p.kps);
       mbar_wait(&bars->empty[s], ph ^ 1u);
-      if (elect_one()) {
-        uint8_t* sb = smem + (size_t)s * stage_bytes + a_bytes;
-        if (p.b_mn_major) {
-          for (int j = 0; j < p.ntile / 32; ++j)
-            tma_load_4d(sb + j * 4096, &map_w, &bars->full[s], nt0 + 32 * j, cb * kKB, tap, 0);
-        } else {
-          tma_load_4d(sb, &map_w, &bars->full[s], cb * kKB, nt0, tap, 0);
+      const bool el = elect_one();
+      for (int u = 0; u < cnt; ++u) {
+        if (el) {
+          uint8_t* sb = smem + (size_t)s * stage_bytes + sb_off + u * b_bytes;
+          if (p.b_mn_major) {
+            for (int j = 0; j < p.ntile / 32; ++j)
+              tma_load_4d(sb + j * 4096, &map_w, &bars->full[s], nt0 + 32 * j, cb * kKB, tap, 0);
+          } else {
+            tma_load_4d(sb, &map_w, &bars->full[s], cb * kKB, nt0, tap, 0);
+          }
         }
+        if (++cb == p.cblocks) { cb = 0; ++tap; }
       }
       __syncwarp();
-      if (++cb == p.cblocks) { cb = 0; ++tap; }
       if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
   }
@@ -254,33 +262,34 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   if (warp == 0) {
     // ================= TMA producer (warp-uniform loop, one elected lane issues) =================
     const int box_rows = p.bw * p.bh * p.bn;
-    const uint32_t tx = (uint32_t)(box_rows * 128 + b_bytes);
+    const uint32_t tx1 = (uint32_t)(box_rows * 128 + b_bytes);          // bytes of one K block (A box + B boxes)
     const int half = p.ksize / 2;
     int s = 0;
     uint32_t ph = 0;
     int tap = k_begin / p.cblocks, cb = k_begin % p.cblocks;
-    for (int i = 0; i < niter; ++i) {
+    for (int i = 0; i < nst; ++i) {
+      const int cnt = min(p.kps, niter - i * p.kps);
       const bool ptr = (p.debug & 8) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512;
       if (ptr && lane == 0) p.trace[i * 4 + 0] = clock64();
       mbar_wait(&bars->empty[s], ph ^ 1u);
-      if (elect_one()) {
+      const bool el = elect_one();
+      if (el) {
         if (ptr) p.trace[i * 4 + 1] = clock64();
         if (!(p.debug & 24) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512) p.trace[i * 4 + 0] = clock64();
-        int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
-        if (p.flip) { dh = -dh; dw = -dw; }
-        uint8_t* sa = smem + (size_t)s * stage_bytes;
-        uint8_t* sb = sa + a_bytes;
-        if (p.debug & 2) {
-          mbar_arrive(&bars->full[s]);
-        } else {
-          mbar_expect_tx(&bars->full[s], tx);      // covers the A box (here) and the B boxes (warp 3)
-          if (ptr) p.trace[i * 4 + 2] = clock64();
-          tma_load_4d(sa, &map_act, &bars->full[s], cb * kKB, w0 + dw, h0 + dh, n0);
-          if (ptr) p.trace[i * 4 + 3] = clock64();
-        }
+        if (p.debug & 2) mbar_arrive(&bars->full[s]);
+        else mbar_expect_tx(&bars->full[s], tx1 * (uint32_t)cnt);   // covers the A boxes (here) and the B boxes (warp 3)
+        if (ptr) p.trace[i * 4 + 2] = clock64();
       }
+      for (int u = 0; u < cnt; ++u) {
+        if (el && !(p.debug & 2)) {
+          int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
+          if (p.flip) { dh = -dh; dw = -dw; }
+          tma_load_4d(smem + (size_t)s * stage_bytes + u * a_bytes, &map_act, &bars->full[s], cb * kKB, w0 + dw, h0 + dh, n0);
+        }
+        if (++cb == p.cblocks) { cb = 0; ++tap; }
+      }
+      if (el && ptr) p.trace[i * 4 + 3] = clock64();
       __syncwarp();
-      if (++cb == p.cblocks) { cb = 0; ++tap; }
       if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
   } else if (warp == 1) {
@@ -289,7 +298,8 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     const uint32_t smem_base = smem_u32(smem);
     int s = 0;
     uint32_t ph = 0;
-    for (int i = 0; i < niter; ++i) {
+    for (int i = 0; i < nst; ++i) {
+      const int cnt = min(p.kps, niter - i * p.kps);
       const bool tr = !(p.debug & 24) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512 && lane == 0;
       if (tr) p.trace[i * 4 + 1] = clock64();
       mbar_wait(&bars->full[s], ph);
@@ -297,20 +307,23 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
       if (tr) p.trace[i * 4 + 2] = clock64();
       tc_fence_after();
       if (elect_one()) {
-        const uint32_t sa = smem_base + (uint32_t)(s * stage_bytes);
-        const uint32_t sb = sa + a_bytes;
+        const uint32_t st0 = smem_base + (uint32_t)(s * stage_bytes);
         if (!(p.debug & 1)) {
+          for (int u = 0; u < cnt; ++u) {
+            const uint32_t sa = st0 + (uint32_t)(u * a_bytes);
+            const uint32_t sb = st0 + (uint32_t)(sb_off + u * b_bytes);
 #pragma unroll
-          for (int k = 0; k < kKB / kUmmaK; ++k) {
-            const uint64_t ad = umma_smem_desc(sa + k * 32, 16, 1024, DDL_UMMA_SW128);
-            const uint64_t bd = p.b_mn_major ? umma_smem_desc(sb + k * 1024, 4096, 512, DDL_UMMA_SW128_BASE32B)
-                                             : umma_smem_desc(sb + k * 32, 16, 1024, DDL_UMMA_SW128);
-            umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < kKB / kUmmaK; ++k) {
+              const uint64_t ad = umma_smem_desc(sa + k * 32, 16, 1024, DDL_UMMA_SW128);
+              const uint64_t bd = p.b_mn_major ? umma_smem_desc(sb + k * 1024, 4096, 512, DDL_UMMA_SW128_BASE32B)
+                                               : umma_smem_desc(sb + k * 32, 16, 1024, DDL_UMMA_SW128);
+              umma_tf32(tmem_base, ad, bd, idesc, (i > 0 || u > 0 || k > 0) ? 1u : 0u);
+            }
           }
         }
         umma_commit(&bars->empty[s]);            // smem slot reusable once these MMAs have read it
-        if (i == niter - 1) umma_commit(&bars->tmem_full);   // accumulator complete
-        if (ptrace && i == niter - 1) p.trace[4] = ddl_globaltimer();
+        if (i == nst - 1) umma_commit(&bars->tmem_full);   // accumulator complete
+        if (ptrace && i == nst - 1) p.trace[4] = ddl_globaltimer();
       }
       __syncwarp();
       if (tr) p.trace[i * 4 + 3] = clock64();
@@ -1025,21 +1038,28 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   p.st = st; p.drop_stream_off = drop_stream_off;
   p.drop_thresh24 = keep_prob >= 1.f ? (1u << 24) : (uint32_t)lrintf(keep_prob * (float)(1 << 24));
   p.drop_inv_keep = keep_prob >= 1.f ? 1.f : 1.f / keep_prob;
-  const int stage_bytes = kTileM * 128 + ntile * 128;
+  // K blocks per stage.  Two halve the barrier round trips, but under the ~110 KB budget that keeps two CTAs per SM
+  // they leave only two stages, and the coarser refill granularity costs more than the saved waits: 356k vs 381k
+  // samples/s for the whole step.  So one is the default and DDL_TC_KPS=2 the experiment (not with the K4
+  // write-through warp, which walks single blocks).
+  const int per_cta_blocks = ceil_div(p.kiters, p.ksplit);
+  p.kps = 1;
+  if (getenv("DDL_TC_KPS") && !p.pull && per_cta_blocks >= 4) p.kps = atoi(getenv("DDL_TC_KPS")) >= 2 ? 2 : 1;
+  const int stage_bytes = p.kps * (kTileM * 128 + ntile * 128);
   // <= ~110 KB of stages: two CTAs per SM stay resident (grids of 150-300 CTAs run as one wave) and
   // 4 stages already cover the ~1000-cycle TMA latency at ~600 cycles per k-iteration
   int stages = (110 * 1024) / stage_bytes;
   if (stages < 2) stages = 2;
   if (stages > kMaxStages) stages = kMaxStages;
-  if (stages > p.kiters) stages = p.kiters < 2 ? 2 : p.kiters;
+  const int fills = ceil_div(per_cta_blocks, p.kps);           // stage fills per CTA
+  if (stages > fills) stages = fills < 2 ? 2 : fills;
   if (getenv("DDL_TC_STAGES")) stages = atoi(getenv("DDL_TC_STAGES"));
   // staged epilogues reuse the stage memory: D (cluster > 1: ntile x 128 floats) + S (128 x (cw + 1) floats)
   size_t epi_bytes = 0;
   if (po) {
     const int cw = ntile / p.cluster;
     epi_bytes = (p.cluster > 1 ? (size_t)ntile * 512 : 0) + (size_t)128 * (cw + 1) * sizeof(float);
-    const int per_cta = ceil_div(p.kiters, p.ksplit);
-    while ((size_t)stages * stage_bytes + stage_bytes <= epi_bytes && stages < kMaxStages && stages < per_cta) ++stages;
+    while ((size_t)stages * stage_bytes + stage_bytes <= epi_bytes && stages < kMaxStages && stages < fills) ++stages;
   }
   p.stages = stages;
   size_t bars_off = (size_t)stages * stage_bytes;
@@ -1121,7 +1141,7 @@ int ddl_tc_plan_unpool_w1grad(DdlTcPlan* pl, const float* x1, float* dw1, int k1
   p.x1 = x1; p.dw1 = dw1; p.k1 = k1;
   if (!store_dfull) p.pool_out = nullptr;
   const size_t patch = (size_t)p.bn * (2 * p.bh + 2 * (k1 / 2)) * (2 * p.bw + 2 * (k1 / 2)) * sizeof(float);
-  const size_t stage_bytes = (size_t)kTileM * 128 + (size_t)p.ntile * 128;
+  const size_t stage_bytes = (size_t)p.kps * ((size_t)kTileM * 128 + (size_t)p.ntile * 128);
   const size_t epi_bytes = (p.cluster > 1 ? (size_t)p.ntile * 512 : 0) + (size_t)128 * (cw + 1) * sizeof(float);
   for (;;) {
     size_t bars_off = (size_t)p.stages * stage_bytes;
@@ -1131,7 +1151,7 @@ int ddl_tc_plan_unpool_w1grad(DdlTcPlan* pl, const float* x1, float* dw1, int k1
     p.aux_off = (int)aux_off;
     pl->smem = aux_off + ((patch + 15) & ~(size_t)15) + (size_t)cw * kW1Pitch + 128 * sizeof(int) + 1024;   // patch, slots, offsets
     // keep two CTAs per SM resident (the patch must not push a ~100 KB pipeline over half an SM): drop a stage instead
-    if (pl->smem <= 110 * 1024 || p.stages <= 3) break;
+    if (pl->smem <= 110 * 1024 || p.stages <= 2) break;
     --p.stages;
   }
   DDL_REQUIRE(pl->smem <= 227 * 1024, "ddl_tc_plan_unpool_w1grad: tile does not fit shared memory");
@@ -1355,6 +1375,8 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages > p.kiters) stages = p.kiters < 2 ? 2 : p.kiters;
   p.stages = stages;
+  p.kps = 1;
+  p.bars_off = stages * stage_bytes;           // the barriers sit right behind the pipeline stages
   pl.smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
   pl.grid = dim3(p.tiles_w * p.tiles_h * p.tiles_n, cout / ntile, ksplit);
   const uint64_t da[4] = {(uint64_t)cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
