@@ -28,6 +28,7 @@ __global__ void step_advance_kernel(DdlStepState* st, float lr, float b1, float 
     st->wstep = ws;
     st->stream = st->stream_base + (ws - 1) * st->stream_stride;
     st->loss_sum = 0.f;
+    st->loss_mean = 0.f;
     st->correct = 0;
     if (advance_opt) {
       const uint32_t t = st->t + 1;
@@ -437,6 +438,7 @@ __global__ void fc3_xent_fwd_kernel(const float* __restrict__ h, const float* __
   float zl = __shfl_sync(0xffffffffu, z, lab >= 0 ? lab : 0);
   if (lane == 0 && st && lab >= 0) {
     atomicAdd(&st->loss_sum, (logf(se) + mx - zl));
+    atomicAdd(&st->loss_mean, (logf(se) + mx - zl) * scale);
     if (am == lab) atomicAdd(&st->correct, 1u);
   }
 }
@@ -656,6 +658,7 @@ __global__ void __launch_bounds__(kFc3Threads) fc3_cluster_kernel(const float* _
     const float zl = __shfl_sync(0xffffffffu, z, lab);
     if (lane == 0) {
       atomicAdd(&st->loss_sum, logf(se) + mx - zl);
+      atomicAdd(&st->loss_mean, (logf(se) + mx - zl) * scale);
       if (am == lab) atomicAdd(&st->correct, 1u);
     }
   }

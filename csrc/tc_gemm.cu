@@ -98,7 +98,10 @@ struct WgradParams {
 };
 
 enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16, EPI_COLSUM = 32,
-       EPI_POOL = 64, EPI_UNPOOL = 128 };
+       EPI_POOL = 64, EPI_UNPOOL = 128,
+       EPI_STAGED = 256 };   // cluster split-K with a fused bias / ReLU / dropout / mask / colsum epilogue: the partial tiles are
+                             // reduce-scattered through distributed shared memory and every CTA finishes its own columns
+                             // (instead of parking them in global scratch for the cluster leader)
 
 struct alignas(8) PipeBars {
   uint64_t full[kMaxStages];
@@ -160,7 +163,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   const int nst = (niter + p.kps - 1) / p.kps;            // pipeline stage fills (kps K blocks each, the last may be short)
   const uint32_t ncols = tmem_cols_for(p.ntile);
   const bool creduce = p.cluster > 1;
-  const bool staged = (p.flags & (EPI_POOL | EPI_UNPOOL)) != 0;
+  const bool staged = (p.flags & (EPI_POOL | EPI_UNPOOL | EPI_STAGED)) != 0;
   const uint32_t crank = creduce ? cluster_ctarank() : 0u;
   const int tile_lin = blockIdx.y * gridDim.x + blockIdx.x;
 
@@ -418,7 +421,8 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
 #pragma unroll
           for (int k = 0; k < 8; ++k)
             if (k < p.cluster) { acc.x += t[k].x; acc.y += t[k].y; acc.z += t[k].z; acc.w += t[k].w; }
-          const float b = ((p.flags & EPI_POOL) && colbase + c < p.nout) ? __ldg(p.bias + colbase + c) : 0.f;
+          const bool addb = (p.flags & EPI_POOL) || ((p.flags & EPI_STAGED) && (p.flags & EPI_BIAS));
+          const float b = (addb && colbase + c < p.nout) ? __ldg(p.bias + colbase + c) : 0.f;
           const int cp = spos(c, cw);
           S[(4 * rg + 0) * sp + cp] = acc.x + b;
           S[(4 * rg + 1) * sp + cp] = acc.y + b;
@@ -429,7 +433,69 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
       named_bar_sync(1, 128);
       const int cq4 = cw >> 2;                   // channel quads per staging row; a thread finishes one quad per item
       float* __restrict__ pout = p.pool_out;
-      if (p.flags & EPI_POOL) {
+      if (p.flags & EPI_STAGED) {
+        // generic fused epilogue on my columns: (bias already added) ReLU, dropout, ReLU/dropout-backward mask, column
+        // sums, float4 stores
+        const int R = p.bw * p.bh * p.bn;
+        const int items = R * cq4;
+        const bool fixed_col = (128 % cq4) == 0;
+        uint32_t seed = 0, stream = 0;
+        if (p.flags & EPI_DROPOUT) { seed = p.st->seed; stream = p.st->stream + p.drop_stream_off; }
+        float csum[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int it = te; it < items; it += 128) {
+          const int c4 = it % cq4, r = it / cq4;
+          const int rw = r % p.bw, rh = (r / p.bw) % p.bh, rn = r / (p.bw * p.bh);
+          const int gw = w0 + rw, gh = h0 + rh, gn = n0 + rn;
+          const int col = colbase + 4 * c4;
+          if (gn >= p.N || gh >= p.H || gw >= p.W || col >= p.nout) continue;
+          const int64_t pix = ((int64_t)gn * p.H + gh) * p.W + gw;
+          const float* sr = S + r * sp + c4;
+          float x[4];
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) x[q4] = sr[q4 * cq4];
+          if (p.flags & EPI_RELU) {
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) x[q4] = fmaxf(x[q4], 0.f);
+          }
+          if (p.flags & EPI_DROPOUT) {
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const uint32_t e = (uint32_t)(pix * p.nout + col + q4);
+              x[q4] = ddl_dropout_keep(seed, stream, e, p.drop_thresh24) ? x[q4] * p.drop_inv_keep : 0.f;
+            }
+          }
+          if (p.flags & EPI_MASKPOS) {
+            const float4 m = *reinterpret_cast<const float4*>(p.mask_act + pix * p.nout + col);
+            x[0] = m.x > 0.f ? x[0] * p.mask_scale : 0.f;
+            x[1] = m.y > 0.f ? x[1] * p.mask_scale : 0.f;
+            x[2] = m.z > 0.f ? x[2] * p.mask_scale : 0.f;
+            x[3] = m.w > 0.f ? x[3] * p.mask_scale : 0.f;
+          }
+          *reinterpret_cast<float4*>(p.out + pix * p.nout + col) = make_float4(x[0], x[1], x[2], x[3]);
+          if (p.flags & EPI_COLSUM) {
+            if (fixed_col) { csum[0] += x[0]; csum[1] += x[1]; csum[2] += x[2]; csum[3] += x[3]; }
+            else {
+#pragma unroll
+              for (int q4 = 0; q4 < 4; ++q4) if (x[q4] != 0.f) atomicAdd(p.colsum + col + q4, x[q4]);
+            }
+          }
+        }
+        if ((p.flags & EPI_COLSUM) && fixed_col) {
+          const bool pow2 = (cq4 & (cq4 - 1)) == 0;
+          if (pow2) {
+            for (int off = cq4; off < 32; off <<= 1) {
+#pragma unroll
+              for (int q4 = 0; q4 < 4; ++q4) csum[q4] += __shfl_xor_sync(0xffffffffu, csum[q4], off);
+            }
+          }
+          const int col = colbase + 4 * (te % cq4);
+          if (!pow2 || cq4 >= 32 || lane < cq4) {
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4)
+              if (csum[q4] != 0.f && col + q4 < p.nout) atomicAdd(p.colsum + col + q4, csum[q4]);
+          }
+        }
+      } else if (p.flags & EPI_POOL) {
         uint8_t* __restrict__ pidx = p.pool_idx;
         const int PH = (p.H + 1) / 2, PW = (p.W + 1) / 2;
         const int pbw = (p.bw + 1) / 2, pbh = (p.bh + 1) / 2;
@@ -1019,6 +1085,13 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   p.cluster = (want_cluster && p.ksplit > 1) ? p.ksplit : 1;
   p.scratch = nullptr;
   p.flags = flags | ((p.ksplit > 1 && p.cluster == 1) ? EPI_ATOMIC : 0);
+  // fused-epilogue cluster plans (the FC layers): reduce-scatter through distributed shared memory, every CTA finishes
+  // ntile / cluster columns.  DDL_TC_LEADER_EPI=1 keeps the older leader-only reduction through global scratch; so do
+  // K4 pull plans and cluster sizes that do not divide the tile into multiples of 4 columns.
+  const bool staged_gen = !po && p.cluster > 1 && fused_epi && !(w_store_dst != nullptr && !dgrad && w_store_dst != w) &&
+                          (p.cluster == 2 || p.cluster == 4 || p.cluster == 8) && ntile % p.cluster == 0 &&
+                          (ntile / p.cluster) % 4 == 0 && getenv("DDL_TC_LEADER_EPI") == nullptr;
+  if (staged_gen) p.flags |= EPI_STAGED;
   p.pool_out = po ? po->out2 : nullptr;
   p.pool_idx = po ? po->idx : nullptr;
   p.dbias = po ? po->dbias : nullptr;
@@ -1056,7 +1129,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   if (getenv("DDL_TC_STAGES")) stages = atoi(getenv("DDL_TC_STAGES"));
   // staged epilogues reuse the stage memory: D (cluster > 1: ntile x 128 floats) + S (128 x (cw + 1) floats)
   size_t epi_bytes = 0;
-  if (po) {
+  if (po || (p.flags & EPI_STAGED)) {
     const int cw = ntile / p.cluster;
     epi_bytes = (p.cluster > 1 ? (size_t)ntile * 512 : 0) + (size_t)128 * (cw + 1) * sizeof(float);
     while ((size_t)stages * stage_bytes + stage_bytes <= epi_bytes && stages < kMaxStages && stages < fills) ++stages;
@@ -1068,7 +1141,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   pl->smem = bars_off + sizeof(PipeBars) + 1024;
   if (pl->smem > 227 * 1024) return (delete pl, fail("tile does not fit shared memory"));
   pl->grid = dim3(p.tiles_w * p.tiles_h * p.tiles_n, ceil_div(nout, ntile), p.ksplit);
-  if (p.cluster > 1 && !po) {
+  if (p.cluster > 1 && !po && !(p.flags & EPI_STAGED)) {
     const size_t bytes = (size_t)pl->grid.x * pl->grid.y * (p.cluster - 1) * kTileM * ntile * sizeof(float);
     if (cudaMalloc((void**)&pl->scratch, bytes) != cudaSuccess) { delete pl; return fail("cudaMalloc(split-K scratch) failed"); }
     p.scratch = pl->scratch;

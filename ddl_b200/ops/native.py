@@ -26,7 +26,8 @@ PAD_VERSION = 33
 class StepState(C.Structure):
     _fields_ = [("t", C.c_uint32), ("lr_t", C.c_float), ("loss_sum", C.c_float), ("correct", C.c_uint32),
                 ("seed", C.c_uint32), ("stream", C.c_uint32), ("wstep", C.c_uint32),
-                ("stream_base", C.c_uint32), ("stream_stride", C.c_uint32), ("pad", C.c_uint32 * 7)]
+                ("stream_base", C.c_uint32), ("stream_stride", C.c_uint32), ("loss_mean", C.c_float),
+                ("pad", C.c_uint32 * 6)]
 
 
 assert C.sizeof(StepState) == 64
@@ -189,7 +190,7 @@ def read_step_state(st: torch.Tensor) -> dict:
     h = st.cpu()
     f = h.view(torch.float32)
     return {"t": int(h[0]), "lr_t": float(f[1]), "loss_sum": float(f[2]), "correct": int(h[3]),
-            "seed": int(h[4]), "stream": int(h[5]), "wstep": int(h[6])}
+            "seed": int(h[4]), "stream": int(h[5]), "wstep": int(h[6]), "loss_mean": float(f[9])}
 
 
 def optimizer_step(opt, p: torch.Tensor, g: torch.Tensor, gscale: float = 1.0, st: Optional[torch.Tensor] = None):

@@ -418,7 +418,9 @@ class FusedTransport(SpmdTransport):
 
     # ------------------------------------------------------------------------------
     def loss(self, batch: int) -> torch.Tensor:
-        return self.st.view(torch.float32)[2] / batch
+        """Mean loss of the latest step: a 0-d VIEW of the device step state (word 9, written by the fc3 kernels
+        with their 1 / batch scale) - no kernel launch; read or copy it before the next step overwrites it."""
+        return self.st.view(torch.float32)[9]
 
     def stats(self) -> Dict[str, object]:
         s = native.read_step_state(self.st)

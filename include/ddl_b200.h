@@ -31,7 +31,8 @@ typedef struct DdlStepState {
   uint32_t wstep;         /* worker steps started                                                */
   uint32_t stream_base;   /* 2 * worker index                                                    */
   uint32_t stream_stride; /* 2 * number of workers: stream = base + (wstep-1) * stride           */
-  uint32_t pad[7];
+  float loss_mean;        /* loss_sum scaled by the kernels' `scale` argument (1 / batch): the step's mean loss   */
+  uint32_t pad[6];
 } DdlStepState;
 
 const char* ddl_last_error(void);
