@@ -29,6 +29,27 @@ def test_launcher_stops_the_job_when_a_rank_dies(tmp_path):
     assert time.time() - t0 < 45
 
 
+def test_launcher_retries_an_early_failure_once(tmp_path):
+    """A job that dies in its first seconds (a taken rendezvous port, a rank killed while importing) is started once
+    more; the second attempt's result is what the caller sees."""
+    vdir = tmp_path / "v"
+    vdir.mkdir()
+    marker = tmp_path / "first_attempt_done"
+    script = ("import os, sys\n"
+              "m = %r\n"
+              "if os.environ.get('RANK') == '0' and not os.path.exists(m):\n"
+              "    open(m, 'w').close()\n"
+              "    sys.exit(5)\n"
+              "sys.exit(0)\n") % str(marker)
+    (vdir / "parameter_server.py").write_text(script)
+    (vdir / "worker.py").write_text(script)
+    from ddl_b200.parallel.launch import launch_with_retry
+    rc = launch_with_retry(str(vdir), 1, 1, ["--device", "cpu"], transport="host", timeout=30, attempts=2)
+    assert rc == 0 and marker.exists()
+    marker.unlink()
+    assert launch_with_retry(str(vdir), 1, 1, ["--device", "cpu"], transport="host", timeout=30, attempts=1) == 5
+
+
 def test_checkpoint_resume_continues_training(tmp_path):
     env = dict(os.environ, OMP_NUM_THREADS="2")
     cwd = os.path.join(ROOT, "mnist_sync")
