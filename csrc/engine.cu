@@ -515,6 +515,17 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   return 0;
 }
 
+/* host-only planning helpers, exposed for tests: the (N tile, cluster) choice of the staged conv plans and of the FC
+ * plans (ntile_cluster[0] = N tile, [1] = cluster / K split) */
+int ddl_plan_pick_staged(int pix_tiles, int nout, int kiters, int* ntile_cluster) {
+  pick_staged_tiling(pix_tiles, nout, kiters, &ntile_cluster[0], &ntile_cluster[1]);
+  return 0;
+}
+int ddl_plan_pick_fc(int nout, int kiters, int* ntile_cluster) {
+  pick_fc_tiling(nout, kiters, &ntile_cluster[0], &ntile_cluster[1]);
+  return 0;
+}
+
 int ddl_engine_set_advance(DdlEngine* e, float lr, float b1, float b2, int advance_opt) {
   DDL_REQUIRE(e != nullptr, "ddl_engine_set_advance: null engine");
   e->own_advance = true;

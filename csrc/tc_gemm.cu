@@ -1467,6 +1467,13 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
   return ddl_maxpool_fwd(raw, bias, y, idx, N, H, W, cout, s);
 }
 
+/* host-only: the TMA pixel box (bw, bh, bn) chosen for an [N, H, W] activation; even_windows = the pooling variant */
+int ddl_plan_choose_box(int N, int H, int W, int max_rows, int row_mult, int even_windows, int* box3) {
+  DDL_REQUIRE(N > 0 && H > 0 && W > 0 && max_rows > 0 && row_mult > 0 && box3 != nullptr, "ddl_plan_choose_box: bad arguments");
+  choose_box(N, H, W, max_rows, row_mult, &box3[0], &box3[1], &box3[2], even_windows != 0);
+  return 0;
+}
+
 /* introspection for tests / profiling notes: fills {grid.x, grid.y, grid.z, stages, smem, bw, bh, bn} */
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8) {
   DDL_REQUIRE(pl != nullptr, "ddl_tc_plan_info: null plan");

@@ -116,6 +116,9 @@ def lib() -> C.CDLL:
         "ddl_tc_plan_dgrad_unpool": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_tc_plan_unpool_w1grad": ([vp, vp, vp, i32, i32], i32),
         "ddl_tc_plan_set_x1": ([vp, vp], i32),
+        "ddl_plan_choose_box": ([i32, i32, i32, i32, i32, i32, C.POINTER(C.c_int)], i32),
+        "ddl_plan_pick_staged": ([i32, i32, i32, C.POINTER(C.c_int)], i32),
+        "ddl_plan_pick_fc": ([i32, i32, C.POINTER(C.c_int)], i32),
         "ddl_tc_plan_run": ([vp, vp], i32),
         "ddl_tc_plan_destroy": ([vp], None),
         "ddl_tc_plan_info": ([vp, C.POINTER(C.c_int)], i32),

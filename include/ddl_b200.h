@@ -137,6 +137,11 @@ DdlTcPlan* ddl_tc_plan_dgrad_unpool(const float* dy, const float* w, const uint8
  * the un-pooled gradient tensor itself.  ddl_tc_plan_set_x1 re-points x1 (alternating input buffers). */
 int ddl_tc_plan_unpool_w1grad(DdlTcPlan* pl, const float* x1, float* dw1, int k1, int store_dfull);
 int ddl_tc_plan_set_x1(DdlTcPlan* pl, const float* x1);
+/* host-only planning helpers (no device needed; used by the CPU tests): pixel box of a plan, (N tile, cluster) choice
+ * of the staged conv plans and of the FC plans */
+int ddl_plan_choose_box(int N, int H, int W, int max_rows, int row_mult, int even_windows, int* box3);
+int ddl_plan_pick_staged(int pix_tiles, int nout, int kiters, int* ntile_cluster);
+int ddl_plan_pick_fc(int nout, int kiters, int* ntile_cluster);
 int ddl_tc_plan_run(const DdlTcPlan* pl, cudaStream_t s);
 void ddl_tc_plan_destroy(DdlTcPlan* pl);
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8);

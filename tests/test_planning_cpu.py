@@ -1,0 +1,84 @@
+"""Host-side planning logic of the native library (no device needed): TMA pixel boxes and the measured
+(N tile, cluster) rules (profiles/pool_fusion.md).  Also proves that the in-tree .so builds and loads on a CPU box."""
+import ctypes as C
+
+import pytest
+
+from ddl_b200.ops import native
+
+
+def _lib():
+    try:
+        return native.lib()
+    except native.NativeError as e:          # no nvcc and no prebuilt library
+        pytest.skip("native library unavailable: %s" % e)
+
+
+def box(N, H, W, max_rows=128, row_mult=1, even=False):
+    out = (C.c_int * 3)()
+    assert _lib().ddl_plan_choose_box(N, H, W, max_rows, row_mult, int(even), out) == 0
+    return tuple(out)
+
+
+def staged(pix, nout, kiters):
+    out = (C.c_int * 2)()
+    assert _lib().ddl_plan_pick_staged(pix, nout, kiters, out) == 0
+    return tuple(out)
+
+
+def test_library_loads_on_cpu_and_reports_version():
+    assert _lib().ddl_version() >= 100
+
+
+@pytest.mark.parametrize("N,H,W", [(100, 14, 14), (100, 7, 7), (100, 4, 4), (37, 14, 14), (513, 4, 4), (10, 28, 28)])
+def test_pixel_boxes_fit_a_tile_and_cover_the_tensor(N, H, W):
+    for even in (False, True):
+        bw, bh, bn = box(N, H, W, even=even)
+        assert 1 <= bw * bh * bn <= 128
+        assert bw == W or W % bw == 0                       # full rows or exact divisors of the width
+        if even:                                            # 2x2 pooling windows never straddle two tiles
+            assert bw == W or bw % 2 == 0
+            assert bh >= H or bh % 2 == 0
+
+
+def test_wgrad_boxes_are_multiples_of_eight_rows():
+    for (N, H, W, cap) in [(100, 14, 14, 48), (100, 7, 7, 56), (100, 4, 4, 40), (100, 1, 1, 128)]:
+        bw, bh, bn = box(N, H, W, max_rows=cap, row_mult=8)
+        assert (bw * bh * bn) % 8 == 0 and bw * bh * bn <= cap
+
+
+def test_staged_tiling_rule_reproduces_the_measured_optima():
+    # (pixel tiles, output channels, K blocks) of the six fused conv kernels of the reference model at batch 100
+    assert staged(175, 64, 25) == (64, 1)        # conv2 fprop + pool
+    assert staged(48, 128, 50) == (128, 4)       # conv3 fprop + pool
+    assert staged(13, 256, 100) == (128, 8)      # conv4 fprop + pool
+    assert staged(168, 32, 50) == (32, 1)        # conv2 dgrad + unpool
+    assert staged(42, 64, 100) == (64, 4)        # conv3 dgrad + unpool
+    assert staged(13, 128, 200) == (64, 8)       # conv4 dgrad + unpool
+
+
+def test_staged_tiling_large_batches_use_the_widest_tile_unsplit():
+    assert staged(1250, 256, 100) == (256, 1)
+    assert staged(2000, 64, 25) == (64, 1)
+    nt, cl = staged(168, 192, 150)               # widened model: no pair fits one wave
+    assert 192 % nt == 0 and cl == 1
+
+
+def test_fc_tiling_spreads_the_weight_stream_over_a_wave():
+    out = (C.c_int * 2)()
+    L = _lib()
+    L.ddl_plan_pick_fc(1024, 32, out)
+    assert tuple(out) == (32, 4)                 # fc1: 32 N tiles x cluster 4 = 128 CTAs
+    L.ddl_plan_pick_fc(512, 32, out)
+    assert tuple(out) == (32, 8)                 # fc2: 16 N tiles x cluster 8
+    L.ddl_plan_pick_fc(6144, 192, out)
+    assert tuple(out) == (32, 1)                 # widened fc1: enough N tiles, no split
+
+
+def test_fc3_fused_kernel_shape_limits():
+    L = _lib()
+    assert L.ddl_fc3_fused_fits(100, 512, 10) == 1
+    assert L.ddl_fc3_fused_fits(256, 2048, 16) in (0, 1)
+    assert L.ddl_fc3_fused_fits(257, 512, 10) == 0      # one row per warp: at most 32 x 8 rows
+    assert L.ddl_fc3_fused_fits(100, 3072, 10) == 0     # k-slice of a CTA is at most 256 columns
+    assert L.ddl_fc3_fused_fits(100, 510, 10) == 0      # K % 4
