@@ -182,7 +182,7 @@ def main() -> int:
     flush = None if a.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     sync_all()
-    l0 = native.LAUNCHES
+    l0 = native.launches()
     for i in range(a.steps):
         if flush is not None:
             flush.fill_(i & 0xFF)
@@ -195,7 +195,7 @@ def main() -> int:
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms = float(t.item())
-    launches = (native.LAUNCHES - l0) if not graph_mode else (launches_per_step or 0) * a.steps
+    launches = (native.launches() - l0) if not graph_mode else (launches_per_step or 0) * a.steps
 
     # ---------------- end-to-end through the public API: H2D every step, loss read on the host every step
     host_loss = torch.zeros(2, dtype=torch.float32).pin_memory()

@@ -27,7 +27,9 @@
 
 namespace {
 
-constexpr int kCommThreads = 512;
+// 128-thread blocks (~5k registers each) fit beside two resident GEMM CTAs on every SM; the 512-thread blocks of round 1
+// only found room on SMs that hosted a single GEMM CTA, so an overlapped bucket crawled until the backward was over
+constexpr int kCommThreads = 128;
 
 // perf experiments: globaltimer stamps of block 0 / thread 0 of the sync kernel (tools/sync_phase.py)
 static int g_cstamps_host = 0;                // passed as a kernel argument: no device-side flag load on the hot path
@@ -106,10 +108,10 @@ DDL_DEVICE float4 opt_apply(float4 pv, float4 gv, float* m, float* v, int64_t i,
 // trip), U = 4 for bandwidth-bound large ones.
 template <int KIND, int U>
 __global__ void __launch_bounds__(kCommThreads)
-sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int stamps_on) {
+sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int stamps_on, const int skip_a) {
   pdl_enter();
   __shared__ uint32_t s_last;
-  const bool cst = stamps_on && blockIdx.x == 0 && threadIdx.x == 0 && a.bucket == 0;
+  const bool cst = stamps_on && blockIdx.x == 0 && threadIdx.x == 0 && a.bucket == stamps_on - 1;
   DDL_CSTAMP(0);
   const uint32_t t = a.st->t;                       // same on every rank: all ranks advance together
   const uint32_t nb = a.nbuckets > 1 ? (uint32_t)a.nbuckets : 1u;
@@ -118,9 +120,23 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
   // The release store is the only fence needed (the explicit fence.sys in front of it cost a second ~4 us
   // MEMBAR.SYS, tools/sync_phase.py).  A single rank has nobody to wait for: no signals, no system fences.
   const bool solo = c.world == 1;
-  if (!solo) {
+  float* myp = c.params[c.rank];
+  const int nsub = a.nsub > 0 ? a.nsub : 1;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (!solo && !skip_a) {                           // skip_a: sync_wait_kernel (previous launch on this stream) did it
     if (blockIdx.x == 0) pad_signal(c, 0, epochA);
     DDL_CSTAMP(1);
+    // while the signals travel: pull this thread's first optimizer-state lines (local HBM, cold after a full step of
+    // other traffic) into L2, so the loads behind the barrier hit
+    {
+      const int64_t rb0 = a.nsub > 0 ? a.sub_begin[0] : a.begin, re0 = a.nsub > 0 ? a.sub_end[0] : a.end;
+      const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+      if (q < (re0 - rb0) / 4 && (threadIdx.x & 7) == 0) {           // one prefetch per 128-byte line
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(myp + rb0 + q * 4));
+        if (KIND >= 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.m + rb0 + q * 4));
+        if (KIND == 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.v + rb0 + q * 4));
+      }
+    }
     pad_wait(c, 0, epochA);                         // every block polls its own (local) pad
     __syncthreads();
   }
@@ -128,9 +144,6 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
 
   constexpr int WCH = (U == 1) ? DDL_MAX_PEERS : 4;  // peers loaded per batch: WCH * U float4 in flight
   const float step = (KIND == 2) ? a.st->lr_t : a.lr;
-  float* myp = c.params[c.rank];
-  const int nsub = a.nsub > 0 ? a.nsub : 1;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int sr = 0; sr < nsub; ++sr) {
   const int64_t rb = a.nsub > 0 ? a.sub_begin[sr] : a.begin, re = a.nsub > 0 ? a.sub_end[sr] : a.end;
   const int64_t n4 = (re - rb) / 4;
@@ -227,14 +240,28 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
   }
   __syncthreads();
   if (s_last) {
-    // every block's fence + counter bump has been observed by this block's thread 0; the release stores below order
-    // them (cumulatively) before the "delivered" signal
-    if (threadIdx.x == 0) *a.done_counter = 0;
+    // Every block's fence + counter bump has been observed by this block's thread 0 through the (relaxed) atomicAdd;
+    // the fence below makes that observation an acquire (fence-fence synchronisation with the other blocks' fences),
+    // bar.sync hands it to the signalling threads, and their release stores order everything (cumulatively) before
+    // the "delivered" signal.
+    if (threadIdx.x == 0) { *a.done_counter = 0; __threadfence_system(); }
     __syncthreads();
     pad_signal(c, 0, epochB);
     pad_wait(c, 0, epochB);
   }
   DDL_CSTAMP(7);
+}
+
+// Barrier A of an OVERLAPPED bucket as its own one-block launch: "my gradients of this bucket are complete" to every
+// rank, then wait for everybody's.  The update kernel behind it is launched with a full (non-programmatic) dependency
+// and skip_a = 1, so none of its blocks is resident - holding threads and registers next to the backward's GEMM
+// kernels - while peers are still computing (round 1 parked 148 x 512 spinning threads there).
+__global__ void __launch_bounds__(32) sync_wait_kernel(const DdlComm c, const DdlSyncArgs a) {
+  pdl_enter();
+  const uint32_t nb = a.nbuckets > 1 ? (uint32_t)a.nbuckets : 1u;
+  const uint32_t epochA = 2u * nb * a.st->t + 2u * (uint32_t)a.bucket + 1u;
+  pad_signal(c, 0, epochA);
+  pad_wait(c, 0, epochA);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -365,11 +392,11 @@ __global__ void device_barrier_kernel(const DdlComm c, uint32_t* epoch_counter) 
 }
 
 int comm_grid(int64_t elems) {
-  // ~2 float4 per thread: the update is a latency-bound stream (7 arena-sized passes), so it wants
-  // every SM's full thread complement (4 x 512) rather than a long grid-stride loop.
+  // ~2 float4 per thread: the update is a latency-bound stream (7 arena-sized passes), so it wants many threads in
+  // flight rather than a long grid-stride loop
   int64_t g = (elems / 4 + 2 * kCommThreads - 1) / (2 * kCommThreads);
   if (g < 1) g = 1;
-  if (g > 148 * 4) g = 148 * 4;
+  if (g > 148 * 16) g = 148 * 16;
   return (int)g;
 }
 
@@ -377,7 +404,7 @@ int comm_grid(int64_t elems) {
 
 extern "C" {
 
-/* perf experiments: enable / read the globaltimer stamps of the sync kernel's block 0 (bucket 0) */
+/* perf experiments: enable (on = bucket + 1, 0 = off) / read the globaltimer stamps of block 0 of that bucket's sync kernel */
 int ddl_comm_stamps(int on, unsigned long long* out, int n) {
   g_cstamps_host = on;
   if (out && n > 0) DDL_CHECK_CUDA(cudaMemcpyFromSymbol(out, g_cstamps, sizeof(unsigned long long) * (n > 16 ? 16 : n)));
@@ -422,21 +449,28 @@ int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, 
     }
   }
   int grid = comm_grid(elems);
-  // a bucket that overlaps the backward spins on its barrier next to compute kernels: keep it narrow
-  static const int cap = getenv("DDL_COMM_CAP") ? atoi(getenv("DDL_COMM_CAP")) : 148;
-  if (a->nbuckets > 1 && a->bucket == 0 && grid > cap) grid = cap;
+  // a bucket that overlaps the backward shares the SMs with the GEMM kernels of the critical chain: keep it narrow
+  static const int cap = getenv("DDL_COMM_CAP") ? atoi(getenv("DDL_COMM_CAP")) : 592;
+  const bool overlapped = a->nbuckets > 1 && a->bucket < a->nbuckets - 1;
+  if (overlapped && grid > cap) grid = cap;
   // bandwidth-bound ranges (>= 16 float4 per thread at the chosen grid): 4 float4 per thread per trip; smaller
   // ranges are latency-bound, and multimem loads measured faster with one (profiles/comm_roofline.md)
   static const int force_u = getenv("DDL_COMM_UNROLL") ? atoi(getenv("DDL_COMM_UNROLL")) : 0;
   const bool wide = force_u ? force_u > 1 : (c->mc_grads == nullptr && elems / 4 >= (int64_t)grid * kCommThreads * 16);
+  int skip_a = 0;
+  if (overlapped && c->world > 1) {
+    DDL_LAUNCH(sync_wait_kernel, 1, 32, 0, s, *c, *a);
+    ddl::no_pdl_once();                    // full dependency: no block of the update kernel is resident during the wait
+    skip_a = 1;
+  }
   if (wide) {
-    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
-    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
-    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
+    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host, skip_a);
+    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host, skip_a);
+    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 4>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host, skip_a);
   } else {
-    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
-    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
-    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host);
+    if (kind == 0) DDL_LAUNCH((sync_push_update_pull_kernel<0, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host, skip_a);
+    else if (kind == 1) DDL_LAUNCH((sync_push_update_pull_kernel<1, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host, skip_a);
+    else DDL_LAUNCH((sync_push_update_pull_kernel<2, 1>), grid, kCommThreads, 0, s, *c, *a, g_cstamps_host, skip_a);
   }
   DDL_LAUNCH_CHECK();
   return 0;

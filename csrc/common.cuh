@@ -42,6 +42,7 @@ bool pdl_enabled();        // DDL_PDL=0 disables programmatic dependent launch
 // weight operands BEFORE griddepcontrol.wait, which is only sound if no earlier kernel that writes weights (the
 // optimizer / pull of the previous step) can still be running - this cuts the chain of early launches there.
 void no_pdl_once();
+void note_launch();   // bumps the counter behind ddl_launch_count()
 // one launch path for every kernel: PDL attribute (+ optional cluster along z)
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
@@ -61,6 +62,7 @@ inline cudaError_t launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_
     ++n;
   }
   cfg.attrs = attr; cfg.numAttrs = n;
+  note_launch();
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 }  // namespace ddl

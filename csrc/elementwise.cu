@@ -282,6 +282,93 @@ __global__ void __launch_bounds__(160) conv1_wgrad_sparse_kernel(const float* __
   if (kh == 0 && db) atomicAdd(db + cg + lane, bsum);
 }
 
+// conv1 weight gradient from the POOLED gradient gp [B, S/2, S/2, C] (the compact output of conv2's dgrad,
+// ddl_tc_plan_dgrad_poolgrad: ReLU-dead windows are already 0) and the argmax slots idx: the un-pooled plane is never
+// built.  Block = one image x 32 channels, 320 threads = 2 window halves x 5 filter rows x 32 channels.
+//   before griddepcontrol.wait: the zero-padded image -> shared memory (an input of the step);
+//   phase 1: gp (float4) and idx (uchar4) of the whole image, one level of coalesced loads, every load issued before
+//            the first shared store -> sg[w][c] (value), so[w][c] (offset of the argmax pixel's top-left tap);
+//   phase 2: thread (half, kh, c) walks its 98 windows: 2 LDS + 5 LDS of x under filter row kh + 5 FMAs each.  The row
+//            pitch XP = S + 6 puts the four possible argmax pixels of a window in four different banks.
+template <int S, int SPLIT>
+__global__ void __launch_bounds__(320) conv1_wgrad_pooled_kernel(const float* __restrict__ x, const float* __restrict__ gp,
+                                                                 const uint8_t* __restrict__ idx, float* __restrict__ dw,
+                                                                 float* __restrict__ db, int B, int C) {
+  pdl_launch_dependents();
+  constexpr int PS = S / 2, XP = S + 6, NW = PS * PS / SPLIT, NV = NW * 8;   // NW windows, NV float4 / uchar4 items per block
+  constexpr int kT = 320, kTrips = (NV + kT - 1) / kT;
+  static_assert((PS * PS) % (2 * SPLIT) == 0, "windows must split evenly");
+  extern __shared__ __align__(16) float ssm[];
+  float* sx = ssm;                                       // [(S + 4)][XP]
+  float* sg = sx + (S + 4) * XP;                         // [NW][32]
+  unsigned short* so = reinterpret_cast<unsigned short*>(sg + NW * 32);   // [NW][32]
+  float* sred = reinterpret_cast<float*>(so + NW * 32);  // [26][32] partial sums of the second half
+  const int n = blockIdx.x / SPLIT, w0 = (blockIdx.x % SPLIT) * NW, cg = blockIdx.y * 32;
+  const int t = threadIdx.x, lane = t & 31, kh = (t >> 5) % 5, half = t / 160;
+  for (int i = t; i < (S + 4) * XP; i += kT) {
+    const int r = i / XP - 2, cc = i % XP - 2;
+    sx[i] = (r >= 0 && r < S && cc >= 0 && cc < S) ? __ldg(x + (int64_t)n * S * S + r * S + cc) : 0.f;
+  }
+  pdl_wait();
+  {
+    float4 g4[kTrips];
+    uchar4 b4[kTrips];
+#pragma unroll
+    for (int u = 0; u < kTrips; ++u) {
+      const int i = u * kT + t;                          // local window = i / 8, channel quad = i % 8
+      g4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      b4[u] = make_uchar4(0, 0, 0, 0);
+      if (i < NV) {
+        const int64_t o = ((int64_t)n * PS * PS + w0 + (i >> 3)) * C + cg + 4 * (i & 7);
+        g4[u] = __ldcg(reinterpret_cast<const float4*>(gp + o));
+        b4[u] = *reinterpret_cast<const uchar4*>(idx + o);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kTrips; ++u) {
+      const int i = u * kT + t;
+      if (i < NV) {
+        const int wl = i >> 3, w = w0 + wl, ph = w / PS, pw = w % PS;
+        const int base = 2 * ph * XP + 2 * pw;
+        const int bb[4] = {b4[u].x & 3, b4[u].y & 3, b4[u].z & 3, b4[u].w & 3};    // dead windows carry g = 0
+        *reinterpret_cast<float4*>(sg + wl * 32 + 4 * (i & 7)) = g4[u];
+        ushort4 ov;
+        ov.x = (unsigned short)(base + (bb[0] >> 1) * XP + (bb[0] & 1));
+        ov.y = (unsigned short)(base + (bb[1] >> 1) * XP + (bb[1] & 1));
+        ov.z = (unsigned short)(base + (bb[2] >> 1) * XP + (bb[2] & 1));
+        ov.w = (unsigned short)(base + (bb[3] >> 1) * XP + (bb[3] & 1));
+        *reinterpret_cast<ushort4*>(so + wl * 32 + 4 * (i & 7)) = ov;
+      }
+    }
+  }
+  __syncthreads();
+  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+  float bsum = 0.f;
+  const float* xk = sx + kh * XP;
+  constexpr int HW = NW / 2;
+#pragma unroll 7
+  for (int w = half * HW; w < (half + 1) * HW; ++w) {
+    const float g = sg[w * 32 + lane];
+    const float* xr = xk + so[w * 32 + lane];
+    acc[0] += g * xr[0]; acc[1] += g * xr[1]; acc[2] += g * xr[2]; acc[3] += g * xr[3]; acc[4] += g * xr[4];
+    bsum += g;
+  }
+  if (half == 1) {
+#pragma unroll
+    for (int kw = 0; kw < 5; ++kw) sred[(kh * 5 + kw) * 32 + lane] = acc[kw];
+    if (kh == 0) sred[25 * 32 + lane] = bsum;
+  }
+  __syncthreads();
+  if (half == 0) {
+#pragma unroll
+    for (int kw = 0; kw < 5; ++kw) {
+      const float v = acc[kw] + sred[(kh * 5 + kw) * 32 + lane];
+      if (v != 0.f) atomicAdd(dw + (kh * 5 + kw) * C + cg + lane, v);
+    }
+    if (kh == 0 && db) atomicAdd(db + cg + lane, bsum + sred[25 * 32 + lane]);
+  }
+}
+
 // ------------------------------------------------------------------------------------ pooling
 // bias + ReLU + 2x2 stride-2 SAME max-pool over NHWC raw conv sums (bias may be NULL when the input
 // is already post-ReLU).  Starting the running max at 0 IS the ReLU.
@@ -826,6 +913,19 @@ int ddl_conv1_wgrad_sparse(const float* x, const float* dy, const uint8_t* idx, 
     attr_done = true;
   }
   DDL_LAUNCH(conv1_wgrad_sparse_kernel<28>, dim3(B, C / 32), 160, smem, s, x, dy, idx, dw, db, B, C);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+int ddl_conv1_wgrad_pooled(const float* x, const float* gp, const uint8_t* idx, float* dw, float* db, int B, int S, int C,
+                           cudaStream_t s) {
+  DDL_REQUIRE(C % 32 == 0 && S == 28, "ddl_conv1_wgrad_pooled: C %% 32 == 0 and S == 28 (got C=%d S=%d)", C, S);
+  // two blocks per image (98 windows each): 200 blocks, two resident per SM - twice the warps per SM of one block per
+  // image, and every SM gets work (100 blocks left 48 SMs idle)
+  constexpr int S28 = 28, SPLIT = 2, NW = 14 * 14 / SPLIT;
+  const size_t smem = (size_t)(S28 + 4) * (S28 + 6) * sizeof(float) + (size_t)NW * 32 * (sizeof(float) + sizeof(unsigned short)) +
+                      26 * 32 * sizeof(float);
+  DDL_LAUNCH((conv1_wgrad_pooled_kernel<28, SPLIT>), dim3(B * SPLIT, C / 32), 320, smem, s, x, gp, idx, dw, db, B, C);
   DDL_LAUNCH_CHECK();
   return 0;
 }

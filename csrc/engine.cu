@@ -18,6 +18,7 @@ namespace {
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
+
 struct FwdPlans {                  // forward plans for one batch size
   int B = 0;
   DdlTcPlan* conv[3] = {nullptr, nullptr, nullptr};    // conv2..conv4
@@ -60,7 +61,7 @@ struct DdlEngine {
   DdlTcPlan* dg_conv[3] = {};
   int dg_split[3] = {1, 1, 1};
   bool dg_unpool[3] = {false, false, false};   // dgrad plan's epilogue is the pool + ReLU backward of the layer below
-  bool w1_fused = false;                       // ... and dg_conv[0] also emits conv1's weight / bias gradient
+  bool w1_pooled = false;                      // dg_conv[0] keeps conv1's gradient in the pooled layout (see build_bwd)
   DdlTcPlan* wg_fc[2] = {};
   DdlTcPlan* dg_fc[2] = {};        // dg_fc[0]: fc1 -> dp4 (cnn only), dg_fc[1]: fc2 -> dh1
   std::vector<void*> allocs;
@@ -68,12 +69,12 @@ struct DdlEngine {
   // optimizer); captured into the step graph as parallel branches
   // backward-overlapped push (gradient bucketing): argument blocks of the bucket launched on the side stream
   DdlComm ov_comm;
-  DdlSyncArgs ov_args[4];
+  DdlSyncArgs ov_args[8];
   int ov_n = 0, ov_kind = 2;
   cudaStream_t side = nullptr;
   cudaStream_t side2 = nullptr;    // the overlapped push/update/pull bucket: must not delay the remaining wgrads
   cudaEvent_t ev_fork[8] = {};
-  cudaEvent_t ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr;
+  cudaEvent_t ev_join = nullptr, ev_fork2 = nullptr, ev_join2 = nullptr, ev_fc_w = nullptr, ev_fc_m = nullptr;
   // one stream per conv weight-gradient kernel: they only depend on their own dY, and serialising them on one
   // stream made that stream the critical path of the backward (tools/timeline.py)
   cudaStream_t wside[2] = {nullptr, nullptr};       // conv3 / conv2 wgrads (conv4 + FC wgrads stay on `side`)
@@ -244,27 +245,19 @@ int build_bwd(DdlEngine* e) {
       pick_staged_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), &nt, &ks);
       ddl_tc_plan_destroy(probe2);
       const int US = e->S[l - 1];
-      e->dg_conv[l - 1] = ddl_tc_plan_dgrad_unpool(e->dfull[l], e->P(v), e->idx[l - 1], e->dfull[l - 1],
-                                                   l - 1 >= 1 ? e->G(v - 1) : nullptr, B, S, S, US, US, cout, cin, 5, nt, ks);
+      if (l == 1 && e->C[0] == 1 && e->S[0] == 28 && cin % 32 == 0) {
+        // conv2's dgrad: conv1 has one input channel and no data gradient, so the un-pooled plane is never built - the
+        // epilogue keeps the gradient in the pooled layout (ReLU-dead windows zeroed, conv1's bias gradient summed) and
+        // ddl_conv1_wgrad_pooled reads value + argmax slot per window (4x fewer bytes, no 75%-zero tensor)
+        e->dg_conv[0] = ddl_tc_plan_dgrad_poolgrad(e->dfull[1], e->P(v), e->idx[0], e->dpool[0], e->G(1), B, S, S, cout, cin,
+                                                   5, nt, ks);
+        e->w1_pooled = e->dg_conv[0] != nullptr;
+      } else {
+        e->dg_conv[l - 1] = ddl_tc_plan_dgrad_unpool(e->dfull[l], e->P(v), e->idx[l - 1], e->dfull[l - 1],
+                                                     l - 1 >= 1 ? e->G(v - 1) : nullptr, B, S, S, US, US, cout, cin, 5, nt, ks);
+      }
       if (!e->dg_conv[l - 1]) return -1;
       e->dg_unpool[l - 1] = true;
-      // conv2's dgrad also produces conv1's weight and bias gradient (conv1 has one input channel): no un-pooled
-      // gradient tensor, no conv1 wgrad kernel at the tail of the step.  x is re-pointed before every run.
-      // Measured (tools/w1_perf.py): the fused pass costs the dgrad kernel ~25 us (128 epilogue threads walk 119 pixels x
-      // 7 taps each) against 18 us for the separate kernel it replaces - neutral in the step, so it is opt-in
-      // (DDL_W1_FUSE=1) and the sparse stand-alone kernel below is the default.
-      static const bool no_w1 = getenv("DDL_W1_FUSE") == nullptr;
-      if (l == 1 && e->C[0] == 1 && !no_w1) {
-        DdlTcPlan* alt = ddl_tc_plan_dgrad_unpool(e->dfull[l], e->P(v), e->idx[0], e->dfull[0], e->G(1), B, S, S, US, US, cout,
-                                                  cin, 5, nt, ks);
-        if (alt && ddl_tc_plan_unpool_w1grad(alt, e->pooled[0], e->G(0), 5, 0) == 0) {
-          ddl_tc_plan_destroy(e->dg_conv[0]);
-          e->dg_conv[0] = alt;
-          e->w1_fused = true;
-        } else if (alt) {
-          ddl_tc_plan_destroy(alt);
-        }
-      }
       continue;
     }
     pick_tiling(pix_tiles_of(probe2), cin, 25 * cdiv(cout, 32), true, &nt, &ks);
@@ -352,7 +345,9 @@ DdlEngine* ddl_engine_create(const DdlEngineCfg* cfg) {
   if (cudaStreamCreateWithFlags(&e->side, cudaStreamNonBlocking) != cudaSuccess) return fail(e, "side stream");
   if (cudaStreamCreateWithFlags(&e->side2, cudaStreamNonBlocking) != cudaSuccess) return fail(e, "side stream 2");
   if (cudaEventCreateWithFlags(&e->ev_fork2, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&e->ev_join2, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
+      cudaEventCreateWithFlags(&e->ev_join2, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_fc_w, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&e->ev_fc_m, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   for (auto& ev : e->ev_fork)
     if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
   if (cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming) != cudaSuccess) return fail(e, "event");
@@ -388,6 +383,8 @@ void ddl_engine_destroy(DdlEngine* e) {
   if (e->ev_join) cudaEventDestroy(e->ev_join);
   if (e->ev_fork2) cudaEventDestroy(e->ev_fork2);
   if (e->ev_join2) cudaEventDestroy(e->ev_join2);
+  if (e->ev_fc_w) cudaEventDestroy(e->ev_fc_w);
+  if (e->ev_fc_m) cudaEventDestroy(e->ev_fc_m);
   if (e->side) cudaStreamDestroy(e->side);
   if (e->side2) cudaStreamDestroy(e->side2);
   for (int i = 0; i < 2; ++i) {
@@ -442,18 +439,34 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     ++fk;
     return 0;
   };
-  // the overlapped push bucket (conv3..fc3) may start once the wgrads of conv3 (its own stream) and of conv4 / fc1 /
-  // fc2 (stream w) are done; the bias gradients come from main-stream kernels that both already waited for
-  // ... and once conv3's dgrad - the last reader of a weight this bucket updates in place - has run on the main stream
-  auto launch_overlap = [&](cudaStream_t after_conv3) -> int {
-    DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork2, after_conv3));
-    DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fork2, 0));
-    if (after_conv3 != w) DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_w0, 0));
-    DDL_CHECK_CUDA(cudaEventRecord(e->ev_main2, s));
-    DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_main2, 0));
+  // Overlapped push buckets (side2 stream, in bucket order on every rank):
+  //   bucket 0 = the FC layers (60% of the bytes): once their weight gradients (stream w) exist and fc1's dgrad - the
+  //              last reader of a weight this bucket updates in place - has run on the main stream;
+  //   bucket 1 = conv3 / conv4: once their weight gradients (wside[0], w) exist and conv3's dgrad has run.
+  // The bias gradients come from main-stream kernels that have run by then.  The caller launches the last bucket
+  // (conv1 / conv2) after the step.
+  auto launch_bucket = [&](int bucket, cudaStream_t bs) -> int {
     for (int i = 0; i < e->ov_n; ++i)
-      if (ddl_sync_push_update_pull(&e->ov_comm, &e->ov_args[i], e->ov_kind, e->side2)) return -1;
-    DDL_CHECK_CUDA(cudaEventRecord(e->ev_join2, e->side2));
+      if (e->ov_args[i].bucket == bucket && ddl_sync_push_update_pull(&e->ov_comm, &e->ov_args[i], e->ov_kind, bs)) return -1;
+    return 0;
+  };
+  auto launch_overlap_fc = [&]() -> int {
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_fc_w, w));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fc_w, 0));
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_fc_m, s));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fc_m, 0));
+    return launch_bucket(0, e->side2);
+  };
+  auto launch_overlap = [&](cudaStream_t after_conv3) -> int {
+    // bucket 1 rides the stream of conv3's weight gradient (its last producer) instead of opening one more parallel
+    // branch in the step graph; bucket 0 (side2) is ordered before it so every rank launches the buckets in one order
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork2, e->side2));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(after_conv3, e->ev_fork2, 0));
+    if (after_conv3 != w) DDL_CHECK_CUDA(cudaStreamWaitEvent(after_conv3, e->ev_w0, 0));
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_main2, s));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(after_conv3, e->ev_main2, 0));
+    if (launch_bucket(1, after_conv3)) return -1;
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_join2, after_conv3));
     return 0;
   };
   if (fork(w)) return -1;
@@ -464,6 +477,7 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   if (ddl_tc_plan_needs_zero(e->dg_fc[0]))             // plain split-K output: partial sums are red.add-ed
     DDL_CHECK_CUDA(cudaMemsetAsync(e->dpool[3], 0, (size_t)B * e->F[0] * sizeof(float), s));
   if (ddl_tc_plan_run(e->dg_fc[0], s)) return -1;
+  if (e->ov_n > 0 && e->nconv && launch_overlap_fc()) return -1;
   int v = 6;
   const bool unpool = e->dg_unpool[0] && e->dg_unpool[1] && e->dg_unpool[2];
   if (unpool) {
@@ -475,7 +489,6 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
       if (fork(wl)) return -1;
       if (ddl_tc_plan_run(e->wg_conv[l - 1], wl)) return -1;
       if (l == 3) DDL_CHECK_CUDA(cudaEventRecord(e->ev_w0, w));
-      if (l == 1 && e->w1_fused && ddl_tc_plan_set_x1(e->dg_conv[0], x)) return -1;
       if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
       if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
     }
@@ -493,15 +506,13 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
   }
   if (!unpool && ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull[0], nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
-  if (!(unpool && e->w1_fused)) {
-    // the sparse (argmax-pixels-only) kernel does a quarter of the arithmetic but is slower inside the step (371k vs
-    // 385k samples/s: one block per image, two dependent load levels) - opt-in with DDL_W1_SPARSE=1
-    static const bool sparse_w1 = getenv("DDL_W1_SPARSE") != nullptr;
-    if (sparse_w1 && e->S[0] == 28 && e->C[1] % 32 == 0) {
-      if (ddl_conv1_wgrad_sparse(x, e->dfull[0], e->idx[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) return -1;
-    } else if (ddl_conv1_wgrad(x, e->dfull[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) {
-      return -1;
-    }
+  if (unpool && e->w1_pooled) {
+    // no programmatic launch here: this kernel's only early work is a 3 KB image load, and launched early its 200 blocks
+    // sat on the SMs next to conv2's dgrad for its whole duration (measured: 0.2222 -> 0.2179 ms per step without)
+    ddl::no_pdl_once();
+    if (ddl_conv1_wgrad_pooled(x, e->dpool[0], e->idx[0], e->G(0), nullptr, B, e->S[0], e->C[1], s)) return -1;
+  } else if (ddl_conv1_wgrad(x, e->dfull[0], e->G(0), e->G(1), B, e->S[0], e->C[1], s)) {
+    return -1;
   }
   DDL_CHECK_CUDA(cudaEventRecord(e->ev_join, w));
   DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join, 0));
@@ -534,7 +545,7 @@ int ddl_engine_set_advance(DdlEngine* e, float lr, float b1, float b2, int advan
 }
 
 int ddl_engine_set_overlap(DdlEngine* e, const DdlComm* c, const DdlSyncArgs* args, int nargs, int kind) {
-  DDL_REQUIRE(e != nullptr && nargs >= 0 && nargs <= 4, "ddl_engine_set_overlap: bad arguments");
+  DDL_REQUIRE(e != nullptr && nargs >= 0 && nargs <= 8, "ddl_engine_set_overlap: bad arguments");
   if (nargs > 0) e->ov_comm = *c;
   for (int i = 0; i < nargs; ++i) e->ov_args[i] = args[i];
   e->ov_n = nargs;

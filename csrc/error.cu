@@ -3,6 +3,7 @@
 #include "../include/ddl_b200.h"
 #include <stdarg.h>
 #include <stdlib.h>
+#include <atomic>
 
 namespace ddl {
 static thread_local char g_err[1024] = "";
@@ -20,10 +21,15 @@ bool pdl_enabled() {
   if (g_no_pdl_once) { g_no_pdl_once = false; return false; }
   return on;
 }
+static std::atomic<unsigned long long> g_launches{0};
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 }  // namespace ddl
 
 extern "C" const char* ddl_last_error(void) { return ddl::get_error(); }
-extern "C" int ddl_version(void) { return 100; }
+extern "C" int ddl_version(void) { return 200; }
+/* kernels launched by this library in this process since it was loaded (every launch goes through ddl::launch; a launch
+ * recorded during stream capture counts once, however often the graph is replayed) */
+extern "C" unsigned long long ddl_launch_count(void) { return ddl::g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int ddl_memcpy_async(void* dst, const void* src, size_t bytes, cudaStream_t s) {
   DDL_CHECK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, s));

@@ -27,6 +27,18 @@
 #include <string.h>
 #include <new>
 
+
+// Lab instrumentation (clock64 / globaltimer traces, skip-MMA / skip-TMA switches used by tools/tc_*.py and
+// tools/wgrad_trace.py) is compiled in only with -DDDL_TC_LAB (ops/build.py --lab -> libddl_b200_lab.so); in the
+// product library both macros are compile-time constants and every instrumented branch disappears.
+#ifdef DDL_TC_LAB
+#define LAB_DEBUG(p) ((p).debug)
+#define LAB_TRACE(p) ((p).trace)
+#else
+#define LAB_DEBUG(p) 0
+#define LAB_TRACE(p) (static_cast<unsigned long long*>(nullptr))
+#endif
+
 namespace {
 
 constexpr int kTileM = 128;        // UMMA M (TMEM lanes)
@@ -34,7 +46,6 @@ constexpr int kKB = 32;            // fp32 elements per K-block = one 128-byte s
 constexpr int kUmmaK = 8;          // tf32: 32 bytes of K per instruction
 constexpr int kThreadsTc = 192;    // 6 warps
 constexpr int kMaxStages = 8;
-constexpr int kW1Pitch = 132;      // bytes per channel row of the argmax-slot stash of the fused first-layer wgrad
 
 struct ActParams {
   // pixel space of the activation operand and of the output
@@ -73,13 +84,6 @@ struct ActParams {
   uint8_t* pool_idx;               // argmax slots: written by EPI_POOL (nullable), read by EPI_UNPOOL
   int UH, UW;                      // EPI_UNPOOL: un-pooled plane (H = ceil(UH/2), W = ceil(UW/2))
   float* dbias;                    // EPI_UNPOOL: += column sums of the routed gradient (nullable)
-  // EPI_UNPOOL + first-layer weight gradient (the layer below has ONE input channel, conv1): the epilogue also
-  // accumulates dW1[tap][c] += g * x1[pixel of the argmax slot + tap offset] - only the argmax slots are non-zero, so
-  // this is 1/4 of the separate kernel's work and needs no second pass over the un-pooled gradient
-  const float* x1;                 // [N, UH, UW] single-channel input of the layer below (nullable = off)
-  float* dw1;                      // [k1*k1][nout]
-  int k1;                          // its filter size
-  int aux_off;                     // byte offset of the x patch + slot stash in shared memory
 };
 
 struct WgradParams {
@@ -99,7 +103,8 @@ struct WgradParams {
 
 enum { EPI_BIAS = 1, EPI_RELU = 2, EPI_DROPOUT = 4, EPI_MASKPOS = 8, EPI_ATOMIC = 16, EPI_COLSUM = 32,
        EPI_POOL = 64, EPI_UNPOOL = 128,
-       EPI_STAGED = 256 };   // cluster split-K with a fused bias / ReLU / dropout / mask / colsum epilogue: the partial tiles are
+       EPI_STAGED = 256,
+       EPI_POOLGRAD = 512 };   // cluster split-K with a fused bias / ReLU / dropout / mask / colsum epilogue: the partial tiles are
                              // reduce-scattered through distributed shared memory and every CTA finishes its own columns
                              // (instead of parking them in global scratch for the cluster leader)
 
@@ -139,8 +144,8 @@ __global__ void __launch_bounds__(kThreadsTc, 1)
 tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_constant__ CUtensorMap map_w,
                    const __grid_constant__ CUtensorMap map_wst, const ActParams p) {
   pdl_launch_dependents();                 // the next kernel may start its prologue now
-  const bool ptrace = (p.debug & 16) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0;
-  if (ptrace && threadIdx.x == 0) p.trace[0] = ddl_globaltimer();
+  const bool ptrace = (LAB_DEBUG(p) & 16) && LAB_TRACE(p) && blockIdx.x + blockIdx.y + blockIdx.z == 0;
+  if (ptrace && threadIdx.x == 0) LAB_TRACE(p)[0] = ddl_globaltimer();
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment by pointer arithmetic on the __shared__ array (an integer round trip would turn every later
   // access into a generic LD.E / ST.E instead of LDS / STS)
@@ -185,29 +190,13 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = bars->tmem_addr;
-  if (ptrace && threadIdx.x == 0) p.trace[1] = ddl_globaltimer();
+  if (ptrace && threadIdx.x == 0) LAB_TRACE(p)[1] = ddl_globaltimer();
   // everything above overlapped the previous kernel; its data (the activation operand) is needed from here.  The
   // weight operand is not produced by the preceding kernels (see ddl::no_pdl_once), so the B producer (warp 3) starts
   // filling the pipeline right away and only joins the wait before its epilogue duty.
-  const bool w1grad = (p.flags & EPI_UNPOOL) && p.x1 != nullptr;
-  // zero-padded patch of the single-channel image under this tile's un-pooled pixels (+ filter halo); x1 is an input
-  // of the step, not an output of the previous kernel, so warps 2, 4, 5 fetch it before the wait
-  const int k1h = p.k1 / 2;
-  const int xpw = 2 * p.bw + 2 * k1h, xph = 2 * p.bh + 2 * k1h;
-  float* xs = reinterpret_cast<float*>(smem + p.aux_off);
-  uint8_t* sidx = reinterpret_cast<uint8_t*>(xs) + (w1grad ? ((p.bn * xph * xpw * 4 + 15) & ~15) : 0);
-  if (w1grad && warp >= 2 && warp != 3 && !(p.debug & 512)) {
-    const int tl = (warp == 2 ? 0 : warp - 3) * 32 + lane;          // 0..95
-    const int total = p.bn * xph * xpw;
-    for (int i = tl; i < total; i += 96) {
-      const int xw = i % xpw, xh = (i / xpw) % xph, xn = i / (xpw * xph);
-      const int gw = 2 * w0 + xw - k1h, gh = 2 * h0 + xh - k1h, gn = n0 + xn;
-      xs[i] = (gn < p.N && gh >= 0 && gh < p.UH && gw >= 0 && gw < p.UW) ? __ldg(p.x1 + ((int64_t)gn * p.UH + gh) * p.UW + gw) : 0.f;
-    }
-  }
   const bool early_b = !p.pull;
   if (!(early_b && warp == 3)) pdl_wait();
-  if (ptrace && threadIdx.x == 0) p.trace[2] = ddl_globaltimer();
+  if (ptrace && threadIdx.x == 0) LAB_TRACE(p)[2] = ddl_globaltimer();
 
   if (warp == 2 && store_through) {
     // ================= K4 store warp: smem weight tile -> local arena (TMA store), before its epilogue duty
@@ -232,7 +221,7 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     __syncwarp();
   }
 
-  if (warp == 3 && !(p.debug & 2)) {
+  if (warp == 3 && !(LAB_DEBUG(p) & 2)) {
     // ================= second TMA producer: the weight (B) boxes.  One UTMALDG of a 128-row box keeps the
     // issuing lane busy for ~200 cycles, so A and B are issued from two warps in parallel; the transaction
     // bytes of both are announced by warp 0's expect_tx (a complete_tx that lands first just drives the
@@ -272,26 +261,26 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     int tap = k_begin / p.cblocks, cb = k_begin % p.cblocks;
     for (int i = 0; i < nst; ++i) {
       const int cnt = min(p.kps, niter - i * p.kps);
-      const bool ptr = (p.debug & 8) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512;
-      if (ptr && lane == 0) p.trace[i * 4 + 0] = clock64();
+      const bool ptr = (LAB_DEBUG(p) & 8) && LAB_TRACE(p) && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512;
+      if (ptr && lane == 0) LAB_TRACE(p)[i * 4 + 0] = clock64();
       mbar_wait(&bars->empty[s], ph ^ 1u);
       const bool el = elect_one();
       if (el) {
-        if (ptr) p.trace[i * 4 + 1] = clock64();
-        if (!(p.debug & 24) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512) p.trace[i * 4 + 0] = clock64();
-        if (p.debug & 2) mbar_arrive(&bars->full[s]);
+        if (ptr) LAB_TRACE(p)[i * 4 + 1] = clock64();
+        if (!(LAB_DEBUG(p) & 24) && LAB_TRACE(p) && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512) LAB_TRACE(p)[i * 4 + 0] = clock64();
+        if (LAB_DEBUG(p) & 2) mbar_arrive(&bars->full[s]);
         else mbar_expect_tx(&bars->full[s], tx1 * (uint32_t)cnt);   // covers the A boxes (here) and the B boxes (warp 3)
-        if (ptr) p.trace[i * 4 + 2] = clock64();
+        if (ptr) LAB_TRACE(p)[i * 4 + 2] = clock64();
       }
       for (int u = 0; u < cnt; ++u) {
-        if (el && !(p.debug & 2)) {
+        if (el && !(LAB_DEBUG(p) & 2)) {
           int dh = tap / p.ksize - half, dw = tap % p.ksize - half;
           if (p.flip) { dh = -dh; dw = -dw; }
           tma_load_4d(smem + (size_t)s * stage_bytes + u * a_bytes, &map_act, &bars->full[s], cb * kKB, w0 + dw, h0 + dh, n0);
         }
         if (++cb == p.cblocks) { cb = 0; ++tap; }
       }
-      if (el && ptr) p.trace[i * 4 + 3] = clock64();
+      if (el && ptr) LAB_TRACE(p)[i * 4 + 3] = clock64();
       __syncwarp();
       if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
@@ -303,15 +292,15 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     uint32_t ph = 0;
     for (int i = 0; i < nst; ++i) {
       const int cnt = min(p.kps, niter - i * p.kps);
-      const bool tr = !(p.debug & 24) && p.trace && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512 && lane == 0;
-      if (tr) p.trace[i * 4 + 1] = clock64();
+      const bool tr = !(LAB_DEBUG(p) & 24) && LAB_TRACE(p) && blockIdx.x + blockIdx.y + blockIdx.z == 0 && i < 512 && lane == 0;
+      if (tr) LAB_TRACE(p)[i * 4 + 1] = clock64();
       mbar_wait(&bars->full[s], ph);
-      if (ptrace && lane == 0 && i == 0) p.trace[3] = ddl_globaltimer();
-      if (tr) p.trace[i * 4 + 2] = clock64();
+      if (ptrace && lane == 0 && i == 0) LAB_TRACE(p)[3] = ddl_globaltimer();
+      if (tr) LAB_TRACE(p)[i * 4 + 2] = clock64();
       tc_fence_after();
       if (elect_one()) {
         const uint32_t st0 = smem_base + (uint32_t)(s * stage_bytes);
-        if (!(p.debug & 1)) {
+        if (!(LAB_DEBUG(p) & 1)) {
           for (int u = 0; u < cnt; ++u) {
             const uint32_t sa = st0 + (uint32_t)(u * a_bytes);
             const uint32_t sb = st0 + (uint32_t)(sb_off + u * b_bytes);
@@ -326,10 +315,10 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
         }
         umma_commit(&bars->empty[s]);            // smem slot reusable once these MMAs have read it
         if (i == nst - 1) umma_commit(&bars->tmem_full);   // accumulator complete
-        if (ptrace && i == nst - 1) p.trace[4] = ddl_globaltimer();
+        if (ptrace && i == nst - 1) LAB_TRACE(p)[4] = ddl_globaltimer();
       }
       __syncwarp();
-      if (tr) p.trace[i * 4 + 3] = clock64();
+      if (tr) LAB_TRACE(p)[i * 4 + 3] = clock64();
       if (++s == p.stages) { s = 0; ph ^= 1u; }
     }
     if (niter == 0 && elect_one()) umma_commit(&bars->tmem_full);
@@ -387,12 +376,12 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     }
     __threadfence();
   }
-  if (ptrace && threadIdx.x == 64) p.trace[5] = ddl_globaltimer();
+  if (ptrace && threadIdx.x == 64) LAB_TRACE(p)[5] = ddl_globaltimer();
   if (creduce) {                             // every thread of every CTA of the cluster
     cluster_arrive_release();
     cluster_wait_acquire();
   }
-  if (ptrace && threadIdx.x == 64) p.trace[6] = ddl_globaltimer();
+  if (ptrace && threadIdx.x == 64) LAB_TRACE(p)[6] = ddl_globaltimer();
   if (staged) {
     if (warp >= 2) {
       // ================= staged epilogue, phases 2 + 3 (warps 2..5, 128 threads)
@@ -549,10 +538,6 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
             bi[u] = make_uchar4(4, 4, 4, 4);
             if (ok[u]) {
               bi[u] = *reinterpret_cast<const uchar4*>(pidx + (((int64_t)gn * p.H + gh[u]) * p.W + gw[u]) * p.nout + colv[u]);
-              if (w1grad) {                      // slot stash [channel][kW1Pitch]: a thread of the wgrad pass reads 4 pixels per LDS
-                uint8_t* sd = sidx + (4 * c4) * kW1Pitch + r;
-                sd[0] = bi[u].x; sd[kW1Pitch] = bi[u].y; sd[2 * kW1Pitch] = bi[u].z; sd[3 * kW1Pitch] = bi[u].w;
-              }
               const float* sr = S + r * sp + c4;
 #pragma unroll
               for (int q4 = 0; q4 < 4; ++q4) g[u][q4] = sr[q4 * cq4];
@@ -563,6 +548,13 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
           for (int u = 0; u < 2; ++u) {
             if (!ok[u]) continue;
             const int b4[4] = {bi[u].x, bi[u].y, bi[u].z, bi[u].w};
+            if (p.flags & EPI_POOLGRAD) {
+              // compact variant (plan sets UH = H, UW = W): the gradient stays in the pooled layout, ReLU-dead windows zeroed (the
+              // layer below has no data gradient, its weight gradient reads value + argmax slot: conv1_wgrad_pooled)
+              *reinterpret_cast<float4*>(pout + ((obase[u] + gh[u]) * p.UW + gw[u]) * p.nout + colv[u]) =
+                  make_float4(b4[0] < 4 ? g[u][0] : 0.f, b4[1] < 4 ? g[u][1] : 0.f, b4[2] < 4 ? g[u][2] : 0.f,
+                              b4[3] < 4 ? g[u][3] : 0.f);
+            } else
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const int uh = 2 * gh[u] + (k >> 1), uw = 2 * gw[u] + (k & 1);
@@ -598,56 +590,6 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
               if (dbsum[q4] != 0.f && col + q4 < p.nout) atomicAdd(p.dbias + col + q4, dbsum[q4]);
           }
         }
-        if (w1grad) {
-          // thread <-> (channel c, tap group): walks every pooled pixel of the tile, one LDS of the gradient and of its
-          // argmax slot, then <= kW1Taps FMAs against the image patch
-          constexpr int kW1Taps = 13;
-          named_bar_sync(1, 128);                      // slot stash complete (S was complete before)
-          const int c = te % cw, tg = te / cw, ngroups = 128 / cw;
-          const int taps1 = p.k1 * p.k1;
-          const int tpg = (taps1 + ngroups - 1) / ngroups;       // taps per group (<= kW1Taps: cw <= 64)
-          const int t0 = tg * tpg;
-          float acc[kW1Taps];
-#pragma unroll
-          for (int j = 0; j < kW1Taps; ++j) acc[j] = 0.f;
-          const int cp = spos(c, cw);
-          int off[kW1Taps];                          // patch offset of each of my taps (no divisions in the pixel loop)
-#pragma unroll
-          for (int j = 0; j < kW1Taps; ++j) {
-            const int tap = t0 + j;
-            off[j] = (j < tpg && tap < taps1) ? (tap / p.k1) * xpw + tap % p.k1 : -1;
-          }
-          // patch offset of every pooled pixel of the tile (-1: outside the tensor), computed once by 128 threads
-          int* roff = reinterpret_cast<int*>(sidx + cw * kW1Pitch);
-          {
-            const int rw = te % p.bw, rh = (te / p.bw) % p.bh, rn = te / (p.bw * p.bh);
-            const bool in = te < R && n0 + rn < p.N && h0 + rh < p.H && w0 + rw < p.W;
-            roff[te] = in ? (rn * xph + 2 * rh) * xpw + 2 * rw : -1;
-          }
-          named_bar_sync(1, 128);
-          // 4 pooled pixels per trip: one LDS.32 of argmax slots, one LDS.128 of patch offsets, then 4 x taps independent
-          // LDS + FMA (dead / outside pixels contribute g = 0 at slot 0)
-          for (int r4 = 0; r4 < ((p.debug & 256) ? 0 : R); r4 += 4) {
-            const uint32_t b4w = *reinterpret_cast<const uint32_t*>(sidx + c * kW1Pitch + r4);
-            const int4 ro = *reinterpret_cast<const int4*>(roff + r4);
-            const int rov[4] = {ro.x, ro.y, ro.z, ro.w};
-#pragma unroll
-            for (int q4 = 0; q4 < 4; ++q4) {
-              const int b = (int)((b4w >> (8 * q4)) & 0xffu);
-              const bool live = b < 4 && rov[q4] >= 0 && r4 + q4 < R;
-              const float g = live ? S[(r4 + q4) * sp + cp] : 0.f;
-              const float* xr = xs + (live ? rov[q4] + (b >> 1) * xpw + (b & 1) : 0);
-#pragma unroll
-              for (int j = 0; j < kW1Taps; ++j)
-                if (off[j] >= 0) acc[j] += g * xr[off[j]];
-            }
-          }
-          if (colbase + c < p.nout && !(p.debug & 128)) {
-#pragma unroll
-            for (int j = 0; j < kW1Taps; ++j)
-              if (off[j] >= 0 && acc[j] != 0.f) atomicAdd(p.dw1 + (int64_t)(t0 + j) * p.nout + colbase + c, acc[j]);
-          }
-        }
       }
     }
     if (creduce) {                           // nobody leaves (or frees its shared memory) while a peer may still read D
@@ -668,20 +610,20 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
     if (p.flags & EPI_DROPOUT) { seed = p.st->seed; stream = p.st->stream + p.drop_stream_off; }
     if (lane == 0) mbar_wait(&bars->tmem_full, 0);      // one poller per warp: 128 threads hammering the
     __syncwarp();                                        // same mbarrier slow the producer / MMA handoffs
-    if (ptrace && threadIdx.x == 64) p.trace[7] = ddl_globaltimer();
+    if (ptrace && threadIdx.x == 64) LAB_TRACE(p)[7] = ddl_globaltimer();
     tc_fence_after();
     const float4* parts = creduce ? reinterpret_cast<const float4*>(p.scratch) +
                                         ((size_t)(tile_lin * (p.cluster - 1)) * (p.ntile / 4)) * 128 + row
                                   : nullptr;
     for (int c0 = 0; c0 < p.ntile; c0 += 16) {
       float v[16];
-      if (p.debug & 64) {
+      if (LAB_DEBUG(p) & 64) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) v[j] = (float)j;
       } else {
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
       }
-      if (ptrace && threadIdx.x == 64 && c0 == 0) p.trace[10] = ddl_globaltimer();
+      if (ptrace && threadIdx.x == 64 && c0 == 0) LAB_TRACE(p)[10] = ddl_globaltimer();
       if (creduce) {                         // add the peers' partial tiles (L2-resident, coalesced)
         if (niter == 0) {
 #pragma unroll
@@ -750,22 +692,22 @@ tc_act_gemm_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_con
           if (lane == j && nt0 + c0 + j < p.nout) atomicAdd(p.colsum + nt0 + c0 + j, sv);
         }
       }
-      if (ptrace && threadIdx.x == 64 && c0 == 0) p.trace[11] = ddl_globaltimer();
-      if (valid && !(p.debug & 32)) {
+      if (ptrace && threadIdx.x == 64 && c0 == 0) LAB_TRACE(p)[11] = ddl_globaltimer();
+      if (valid && !(LAB_DEBUG(p) & 32)) {
 #pragma unroll
         for (int j = 0; j < 16; j += 4) {
           if (nt0 + c0 + j < p.nout)
             *reinterpret_cast<float4*>(orow + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
         }
       }
-      if (ptrace && threadIdx.x == 64 && c0 == 0) p.trace[12] = ddl_globaltimer();
+      if (ptrace && threadIdx.x == 64 && c0 == 0) LAB_TRACE(p)[12] = ddl_globaltimer();
     }
   }
-  if (ptrace && threadIdx.x == 64) p.trace[8] = ddl_globaltimer();
+  if (ptrace && threadIdx.x == 64) LAB_TRACE(p)[8] = ddl_globaltimer();
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, ncols);
-  if (ptrace && threadIdx.x == 32) p.trace[9] = ddl_globaltimer();
+  if (ptrace && threadIdx.x == 32) LAB_TRACE(p)[9] = ddl_globaltimer();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -806,8 +748,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   const int niter = max(0, t_end - t_begin);
   const int ctot = ntap * p.ntile;                        // accumulator columns in use
   const uint32_t ncols = ctot <= 32 ? 32u : ctot <= 64 ? 64u : ctot <= 128 ? 128u : ctot <= 256 ? 256u : 512u;
-  const bool wtrace = p.trace != nullptr && blockIdx.x + blockIdx.y + blockIdx.z == 0;
-  if (wtrace && threadIdx.x == 0) p.trace[520] = clock64();
+  const bool wtrace = LAB_TRACE(p) != nullptr && blockIdx.x + blockIdx.y + blockIdx.z == 0;
+  if (wtrace && threadIdx.x == 0) LAB_TRACE(p)[520] = clock64();
   const int a_live = min(kTileM / 32, (p.ca - a0 + 31) / 32);     // boxes that hold real channels
   const int b_live = min(b_boxes, (p.cb - b0 + 31) / 32);
 
@@ -840,7 +782,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     for (int i = 0; i < niter; ++i) {
       mbar_wait(&bars->empty[s], ph ^ 1u);
       if (elect_one()) {
-        if (wtrace && pidx == 0 && i < 64) p.trace[i * 8 + 0] = clock64();
+        if (wtrace && pidx == 0 && i < 64) LAB_TRACE(p)[i * 8 + 0] = clock64();
         const int t = t_begin + i;
         const int tw = t % p.tiles_w, th = (t / p.tiles_w) % p.tiles_h, tn = t / (p.tiles_w * p.tiles_h);
         const int w0 = tw * p.bw, h0 = th * p.bh, n0 = tn * p.bn;
@@ -857,7 +799,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
             tma_load_4d(sb + (tt * b_boxes + j) * box_bytes, &map_x, &bars->full[s], b0 + 32 * j, w0 + dw, h0 + dh, n0);
           }
         }
-        if (wtrace && pidx == 0 && i < 64) p.trace[i * 8 + 1] = clock64();
+        if (wtrace && pidx == 0 && i < 64) LAB_TRACE(p)[i * 8 + 1] = clock64();
       }
       __syncwarp();
       if (++s == p.stages) { s = 0; ph ^= 1u; }
@@ -873,11 +815,11 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     int s = 0;
     uint32_t ph = 0;
     for (int i = 0; i < niter; ++i) {
-      if (wtrace && i < 64 && lane == 0) p.trace[i * 8 + 2] = clock64();
+      if (wtrace && i < 64 && lane == 0) LAB_TRACE(p)[i * 8 + 2] = clock64();
       mbar_wait(&bars->full[s], ph);
       tc_fence_after();
       if (elect_one()) {
-        if (wtrace && i < 64) p.trace[i * 8 + 3] = clock64();
+        if (wtrace && i < 64) LAB_TRACE(p)[i * 8 + 3] = clock64();
         const uint32_t sa = smem_base + (uint32_t)(s * stage_bytes);
         const uint32_t sb = sa + (uint32_t)(p.a_alloc * box_bytes);
         for (int k = 0; k < ksteps; ++k) {
@@ -893,7 +835,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
         }
         umma_commit(&bars->empty[s]);
         if (i == niter - 1) umma_commit(&bars->tmem_full);
-        if (wtrace && i < 64) p.trace[i * 8 + 4] = clock64();
+        if (wtrace && i < 64) LAB_TRACE(p)[i * 8 + 4] = clock64();
       }
       __syncwarp();
       if (++s == p.stages) { s = 0; ph ^= 1u; }
@@ -903,11 +845,10 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
   } else {
     const int q = warp & 3;
     const int a = a0 + q * 32 + lane;
-    const bool valid = a < p.ca && niter > 0;
     if (lane == 0) mbar_wait(&bars->tmem_full, 0);
     __syncwarp();
     tc_fence_after();
-    if (wtrace && threadIdx.x == 64) p.trace[521] = clock64();
+    if (wtrace && threadIdx.x == 64) LAB_TRACE(p)[521] = clock64();
     // out[tap][b][a]: `a` (this lane's TMEM row) is the contiguous index.  A 4x4 register transpose inside
     // each quad of lanes turns 16 scalar reds per lane into 4 x red.global.add.v4.f32 on 4 consecutive a.
     const int ql = lane & 3;
@@ -941,10 +882,10 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant
     }
   }
   tc_fence_before();
-  if (wtrace && threadIdx.x == 64) p.trace[522] = clock64();
+  if (wtrace && threadIdx.x == 64) LAB_TRACE(p)[522] = clock64();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, ncols);
-  if (wtrace && threadIdx.x == 0) p.trace[523] = clock64();
+  if (wtrace && threadIdx.x == 0) LAB_TRACE(p)[523] = clock64();
 }
 
 // ------------------------------------------------------------------------------------------------ host
@@ -1096,14 +1037,16 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   p.pool_idx = po ? po->idx : nullptr;
   p.dbias = po ? po->dbias : nullptr;
   p.UH = po ? po->UH : 0; p.UW = po ? po->UW : 0;
-  p.x1 = nullptr; p.dw1 = nullptr; p.k1 = 0; p.aux_off = 0;
   p.pull = (w_store_dst != nullptr && !dgrad && w_store_dst != w) ? 1 : 0;
-  p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
+  p.debug = 0;
   p.trace = nullptr;
+#ifdef DDL_TC_LAB
+  p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
   if (getenv("DDL_TC_TRACE")) {
-    cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long));
+    if (cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long)) != cudaSuccess) { delete pl; return fail("cudaMalloc(trace) failed"); }
     cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
   }
+#endif
   p.out = out; p.bias = bias; p.mask_act = mask_act; p.mask_scale = mask_scale;
   p.colsum = colsum;
   if (colsum) p.flags |= EPI_COLSUM;
@@ -1200,41 +1143,16 @@ DdlTcPlan* ddl_tc_plan_dgrad_unpool(const float* dy, const float* w, const uint8
                        1.f, nullptr, nullptr, &po);
 }
 
-/* Adds the weight gradient of a ONE-input-channel layer below (conv1) to a dgrad_unpool plan: dw1[k1*k1][cin] +=
- * sum over the routed gradient's non-zero (argmax) pixels of g * x1[pixel + tap offset]; x1 is [N, UH, UW].
- * store_dfull = 0 additionally drops the un-pooled gradient itself (nothing else consumes it then).
- * ddl_tc_plan_set_x1 re-points x1 before a run (the engine alternates input buffers). */
-int ddl_tc_plan_unpool_w1grad(DdlTcPlan* pl, const float* x1, float* dw1, int k1, int store_dfull) {
-  DDL_REQUIRE(pl && pl->kind == 0 && (pl->act.flags & EPI_UNPOOL), "ddl_tc_plan_unpool_w1grad: not a dgrad_unpool plan");
-  ActParams& p = pl->act;
-  const int cw = p.ntile / p.cluster;
-  DDL_REQUIRE(cw <= 64 && 128 % cw == 0 && k1 >= 1 && (k1 & 1) && k1 * k1 <= 13 * (128 / cw),
-              "ddl_tc_plan_unpool_w1grad: N tile / cluster = %d and filter %d not supported", cw, k1);
-  DDL_REQUIRE(x1 != nullptr && dw1 != nullptr, "ddl_tc_plan_unpool_w1grad: null pointer");
-  p.x1 = x1; p.dw1 = dw1; p.k1 = k1;
-  if (!store_dfull) p.pool_out = nullptr;
-  const size_t patch = (size_t)p.bn * (2 * p.bh + 2 * (k1 / 2)) * (2 * p.bw + 2 * (k1 / 2)) * sizeof(float);
-  const size_t stage_bytes = (size_t)p.kps * ((size_t)kTileM * 128 + (size_t)p.ntile * 128);
-  const size_t epi_bytes = (p.cluster > 1 ? (size_t)p.ntile * 512 : 0) + (size_t)128 * (cw + 1) * sizeof(float);
-  for (;;) {
-    size_t bars_off = (size_t)p.stages * stage_bytes;
-    if (epi_bytes > bars_off) bars_off = (epi_bytes + 15) & ~(size_t)15;
-    p.bars_off = (int)bars_off;
-    const size_t aux_off = (bars_off + sizeof(PipeBars) + 15) & ~(size_t)15;
-    p.aux_off = (int)aux_off;
-    pl->smem = aux_off + ((patch + 15) & ~(size_t)15) + (size_t)cw * kW1Pitch + 128 * sizeof(int) + 1024;   // patch, slots, offsets
-    // keep two CTAs per SM resident (the patch must not push a ~100 KB pipeline over half an SM): drop a stage instead
-    if (pl->smem <= 110 * 1024 || p.stages <= 2) break;
-    --p.stages;
-  }
-  DDL_REQUIRE(pl->smem <= 227 * 1024, "ddl_tc_plan_unpool_w1grad: tile does not fit shared memory");
-  return 0;
-}
-
-int ddl_tc_plan_set_x1(DdlTcPlan* pl, const float* x1) {
-  DDL_REQUIRE(pl && pl->kind == 0 && pl->act.x1 != nullptr && x1 != nullptr, "ddl_tc_plan_set_x1: plan has no fused first-layer wgrad");
-  pl->act.x1 = x1;
-  return 0;
+/* conv dgrad whose epilogue is only the ReLU part of the pool backward: gp[N, H, W, cin] = dgrad value where the window
+ * below is alive (idx < 4), 0 where it is ReLU-dead; dbias += column sums.  For the layer above conv1, whose un-pooled
+ * gradient nobody needs: ddl_conv1_wgrad_pooled consumes gp + idx directly (4x fewer bytes than the un-pooled plane). */
+DdlTcPlan* ddl_tc_plan_dgrad_poolgrad(const float* dy, const float* w, const uint8_t* idx, float* gp, float* dbias,
+                                      int N, int H, int W, int cout, int cin, int ksize, int ntile, int cluster) {
+  PoolOpt po = {gp, const_cast<uint8_t*>(idx), dbias, H, W};
+  DdlTcPlan* pl = plan_act_impl(1, dy, w, nullptr, N, H, W, cout, cin, ksize, ntile, cluster, 0, nullptr, nullptr, 1.f, nullptr,
+                                0, 1.f, nullptr, nullptr, &po);
+  if (pl) pl->act.flags |= EPI_POOLGRAD;
+  return pl;
 }
 
 DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, int H, int W, int ca, int cb,
@@ -1307,10 +1225,12 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   p.stages = stages;
   p.out = out;
   p.trace = nullptr;
+#ifdef DDL_TC_LAB
   if (getenv("DDL_TC_TRACE")) {
-    cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long));
+    if (cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long)) != cudaSuccess) { delete pl; return fail("cudaMalloc(trace) failed"); }
     cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
   }
+#endif
   pl->smem = (size_t)stages * stage_bytes + sizeof(PipeBars) + 1024;
   pl->grid = dim3(p.tgroups, p.mtiles * p.ntiles, p.psplit);
   const uint64_t dg[4] = {(uint64_t)ca, (uint64_t)W, (uint64_t)H, (uint64_t)N};
@@ -1462,6 +1382,9 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
   // split-K partial sums are added with red.add, so the region must start at zero; the array still
   // holds whatever the previous call left there
   if (ksplit > 1) DDL_CHECK_CUDA(cudaMemsetAsync(raw, 0, need, s));
+  // the kernel prefetches weight tiles before griddepcontrol.wait; launched without the programmatic-launch attribute it
+  // starts only after everything earlier on the stream (e.g. an optimizer kernel of this library writing `w`) is done
+  ddl::no_pdl_once();
   DDL_LAUNCH(tc_act_gemm_kernel, pl.grid, kThreadsTc, pl.smem, s, pl.map_a, pl.map_b, pl.map_b, pl.act);
   DDL_LAUNCH_CHECK();
   return ddl_maxpool_fwd(raw, bias, y, idx, N, H, W, cout, s);

@@ -71,11 +71,6 @@ class NativeBackend:
         advanced (``advance_state``) by the caller."""
         native.check(self.L.ddl_engine_train_step(self.h, native.ptr(x), native.ptr(y), native.stream_ptr()),
                      "ddl_engine_train_step")
-        # engine kernels per step: 19 (pools fused into the conv / dgrad epilogues, one fc3 kernel; 18 with conv1's wgrad
-        # inside conv2's dgrad, DDL_W1_FUSE=1), 26 with DDL_NO_POOL_FUSE
-        # (+ the overlapped push bucket)
-        n = 26 if os.environ.get("DDL_NO_POOL_FUSE") else 19 + bool(os.environ.get("DDL_FC3_SPLIT")) - bool(os.environ.get("DDL_W1_FUSE"))
-        native.count(n + getattr(self, "overlap_launches", 0))
 
     def advance_state(self, advance_opt: bool = True) -> None:
         c = self.cfg
@@ -109,7 +104,6 @@ class NativeBackend:
             native.check(self.L.ddl_engine_eval(self.h, x[b:e].data_ptr(), y[b:e].data_ptr(), e - b,
                                                 self._correct.data_ptr(), None, native.stream_ptr()),
                          "ddl_engine_eval")
-            native.count(11 if os.environ.get("DDL_NO_POOL_FUSE") else 8)
         return int(self._correct.item()), n
 
     @torch.no_grad()

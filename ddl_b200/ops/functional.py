@@ -74,10 +74,8 @@ def conv5x5_relu_pool(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, ntil
 
 
 def conv5x5_dgrad_unpool(dy: torch.Tensor, w: torch.Tensor, idx: torch.Tensor, UH: int, UW: int, ntile: int = 0,
-                         cluster: int = 1, want_db: bool = True, x1: Optional[torch.Tensor] = None, k1: int = 5,
-                         store_dfull: bool = True):
-    """conv dgrad + pool/ReLU backward of the layer below in ONE kernel; returns (dfull [N,UH,UW,Cin], dbias) and, with
-    ``x1`` ([N,UH,UW], the single-channel input of the layer below), also that layer's weight gradient [k1,k1,1,Cin]."""
+                         cluster: int = 1, want_db: bool = True):
+    """conv dgrad + pool/ReLU backward of the layer below in ONE kernel; returns (dfull [N,UH,UW,Cin], dbias)."""
     N, H, W, Cout = dy.shape
     k, Cin = w.shape[0], w.shape[2]
     nt = ntile or min(128, Cin)
@@ -85,18 +83,23 @@ def conv5x5_dgrad_unpool(dy: torch.Tensor, w: torch.Tensor, idx: torch.Tensor, U
     db = torch.zeros(Cin, device=dy.device, dtype=torch.float32) if want_db else None
     plan = native.lib().ddl_tc_plan_dgrad_unpool(native.ptr(dy), native.ptr(w), native.ptr(idx), native.ptr(out),
                                                  native.ptr(db), N, H, W, UH, UW, Cout, Cin, k, nt, cluster)
-    if x1 is None:
-        _run_plan(plan)
-        return out, db
-    if not plan:
-        raise native.NativeError("plan creation failed: " + native.last_error())
-    dw1 = torch.zeros(k1, k1, 1, Cin, device=dy.device, dtype=torch.float32)
-    rc = native.lib().ddl_tc_plan_unpool_w1grad(plan, native.ptr(x1), native.ptr(dw1), k1, 1 if store_dfull else 0)
-    if rc:
-        native.lib().ddl_tc_plan_destroy(plan)
-        native.check(rc, "ddl_tc_plan_unpool_w1grad")
     _run_plan(plan)
-    return (out if store_dfull else None), db, dw1
+    return out, db
+
+
+def conv5x5_dgrad_poolgrad(dy: torch.Tensor, w: torch.Tensor, idx: torch.Tensor, ntile: int = 0, cluster: int = 1,
+                           want_db: bool = True):
+    """conv dgrad + the ReLU half of the pool backward, gradient kept in the pooled layout: returns
+    (gp [N,H,W,Cin] with ReLU-dead windows zeroed, dbias)."""
+    N, H, W, Cout = dy.shape
+    k, Cin = w.shape[0], w.shape[2]
+    nt = ntile or min(128, Cin)
+    out = torch.empty(N, H, W, Cin, device=dy.device, dtype=torch.float32)
+    db = torch.zeros(Cin, device=dy.device, dtype=torch.float32) if want_db else None
+    plan = native.lib().ddl_tc_plan_dgrad_poolgrad(native.ptr(dy), native.ptr(w), native.ptr(idx), native.ptr(out),
+                                                   native.ptr(db), N, H, W, Cout, Cin, k, nt, cluster)
+    _run_plan(plan)
+    return out, db
 
 
 def conv5x5_wgrad(dy: torch.Tensor, x: torch.Tensor, ksize: int = 5, ntile: int = 0, psplit: int = 1,
@@ -184,6 +187,17 @@ def conv1_wgrad_sparse(x: torch.Tensor, dy: torch.Tensor, idx: torch.Tensor):
     native.check(native.lib().ddl_conv1_wgrad_sparse(native.ptr(x), native.ptr(dy), native.ptr(idx), native.ptr(dw),
                                                      native.ptr(db), B, S, Cc, native.stream_ptr()), "conv1_wgrad_sparse")
     native.count()
+    return dw, db
+
+
+def conv1_wgrad_pooled(x: torch.Tensor, gp: torch.Tensor, idx: torch.Tensor, want_db: bool = True):
+    """conv1 weight (/ bias) gradient from the pooled gradient ``gp`` [B,S/2,S/2,C] and the argmax slots ``idx``."""
+    B, S = x.shape[0], x.shape[1]
+    Cc = gp.shape[-1]
+    dw = torch.zeros(5, 5, 1, Cc, device=x.device, dtype=torch.float32)
+    db = torch.zeros(Cc, device=x.device, dtype=torch.float32) if want_db else None
+    native.check(native.lib().ddl_conv1_wgrad_pooled(native.ptr(x), native.ptr(gp), native.ptr(idx), native.ptr(dw),
+                                                     native.ptr(db), B, S, Cc, native.stream_ptr()), "conv1_wgrad_pooled")
     return dw, db
 
 

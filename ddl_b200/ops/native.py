@@ -65,7 +65,6 @@ class EngineCfg(C.Structure):
 
 
 _LIB: Optional[C.CDLL] = None
-LAUNCHES = 0          # kernels launched through this binding (bench.py reports it)
 
 
 class NativeError(RuntimeError):
@@ -96,11 +95,13 @@ def lib() -> C.CDLL:
     vp, i32, i64, u32, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_uint32, C.c_float
     sigs = {
         "ddl_version": ([], i32),
+        "ddl_launch_count": ([], C.c_uint64),
         "ddl_step_advance": ([vp, f32, f32, f32, i32, vp], i32),
         "ddl_optimizer_step": ([i32, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, vp, vp], i32),
         "ddl_conv1_relu_pool": ([vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
         "ddl_conv1_wgrad": ([vp, vp, vp, vp, i32, i32, i32, vp], i32),
         "ddl_conv1_wgrad_sparse": ([vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
+        "ddl_conv1_wgrad_pooled": ([vp, vp, vp, vp, vp, i32, i32, i32, vp], i32),
         "ddl_maxpool_fwd": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], i32),
         "ddl_maxpool_bwd": ([vp, vp, vp, vp, i32, i32, i32, i32, vp], i32),
         "ddl_colsum": ([vp, vp, i32, i32, vp], i32),
@@ -114,8 +115,7 @@ def lib() -> C.CDLL:
         "ddl_tc_plan_wgrad": ([vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_tc_plan_conv_pool": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_tc_plan_dgrad_unpool": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32], vp),
-        "ddl_tc_plan_unpool_w1grad": ([vp, vp, vp, i32, i32], i32),
-        "ddl_tc_plan_set_x1": ([vp, vp], i32),
+        "ddl_tc_plan_dgrad_poolgrad": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32], vp),
         "ddl_plan_choose_box": ([i32, i32, i32, i32, i32, i32, C.POINTER(C.c_int)], i32),
         "ddl_plan_pick_staged": ([i32, i32, i32, C.POINTER(C.c_int)], i32),
         "ddl_plan_pick_fc": ([i32, i32, C.POINTER(C.c_int)], i32),
@@ -172,9 +172,14 @@ def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return t.data_ptr()
 
 
+def launches() -> int:
+    """Kernels launched by the native library in this process so far: counted inside the library, in the one launch
+    path every kernel uses (``ddl::launch``).  A launch recorded during stream capture counts once."""
+    return int(lib().ddl_launch_count())
+
+
 def count(n: int = 1) -> None:
-    global LAUNCHES
-    LAUNCHES += n
+    """Kept for callers of the round-1 binding: launches are counted natively now (``launches()``)."""
 
 
 # --------------------------------------------------------------------------------------- helpers

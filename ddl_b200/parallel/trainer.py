@@ -192,13 +192,14 @@ class SPMDTrainer:
             self._ev_ready = [torch.cuda.Event() for _ in range(nslots)]     # slot filled by the copy stream
             self._ev_free = [torch.cuda.Event() for _ in range(nslots)]      # slot's last consumer (a graph replay) enqueued
             self._slot_cnt = [None] * nslots                                 # batch index prefetched into each slot
+            self._slot_prefetched = [False] * nslots                         # a prefetch was ever issued to the slot
             self._slot = 0
             self._nb_local = max(1, self.data.batches_per_epoch(cfg.batch_size, lay.num_workers, cfg.replicate_data))
         torch.cuda.synchronize()
         from ..ops import native
         self._graphs = []
         for slot in range(nslots):
-            l0 = native.LAUNCHES
+            l0 = native.launches()
             g = torch.cuda.CUDAGraph()
             # the main stream of the capture carries the critical chain (forward, dgrads); the engine's side streams
             # (wgrads, overlapped push) have the lowest priority, so a higher-priority capture stream lets the
@@ -212,7 +213,7 @@ class SPMDTrainer:
                 self.transport.step()
             self._graphs.append(g)
             if slot == 0:
-                self.launches_per_step = native.LAUNCHES - l0      # kernels of ours inside one replay
+                self.launches_per_step = native.launches() - l0      # kernels of ours inside one replay
         self._graph = self._graphs[0]
         # the captures themselves did not execute anything; global_step is untouched
 
@@ -233,7 +234,12 @@ class SPMDTrainer:
         if self._slot_cnt[slot] == cnt:
             main.wait_event(self._ev_ready[slot])        # prefetched while the previous step ran
         else:
-            self._h2d(slot, cnt)                          # first step / out-of-order batch index: copy in line
+            # first step / out-of-order batch index: copy in line.  A prefetch of some other batch into this slot may
+            # still be in flight on the copy stream; order this copy behind it, or the slot could end up holding the
+            # prefetched batch
+            if self._slot_prefetched[slot]:
+                main.wait_event(self._ev_ready[slot])
+            self._h2d(slot, cnt)
         self._graphs[slot].replay()
         self._ev_free[slot].record(main)
         # prefetch the next batch of the epoch into the other slot, underneath this step's graph
@@ -243,6 +249,7 @@ class SPMDTrainer:
             self._h2d(nslot, nxt)
             self._ev_ready[nslot].record(self._copy_stream)
         self._slot_cnt[nslot] = nxt
+        self._slot_prefetched[nslot] = True
         self._slot_cnt[slot] = None
         self._slot = nslot
         self.global_step += 1

@@ -115,20 +115,32 @@ class MulticastMemory:
 
 
 def _alloc_arena(nbytes: int, rank: int, world: int, device: torch.device, want_mc: str):
-    """Multicast-capable allocation when asked for (and possible), else plain cudaIpc peer mapping."""
+    """Multicast-capable allocation when asked for (and possible), else plain cudaIpc peer mapping.
+
+    Every rank takes the same path: a constructor failure on one rank is caught locally and turned into a vote, and
+    the MIN all-reduce of the votes always runs, so no rank can skip a collective the others are waiting in."""
     if world > 1 and want_mc in ("auto", "on"):
+        m, why = None, ""
         try:
             m = MulticastMemory(nbytes, rank, world, device)
-            ok = torch.tensor([1 if m.mc else 0], device=device)
-            dist.all_reduce(ok, op=dist.ReduceOp.MIN)       # all ranks or none
-            if int(ok.item()) == 1:
-                return m
+            if not m.mc:
+                why = "no multicast pointer"
+        except Exception as e:                               # noqa: BLE001 - any failure means "no NVLS on this rank"
+            m, why = None, repr(e)
+        ok = torch.tensor([1 if (m is not None and m.mc) else 0], device=device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)           # all ranks or none
+        if int(ok.item()) == 1:
+            return m
+        if m is not None:
             m.close()
-        except Exception as e:                               # noqa: BLE001 - any failure means "no NVLS here"
-            if want_mc == "on":
-                raise native.NativeError("NVLS multicast requested but unavailable: %r" % (e,))
         if want_mc == "on":
-            raise native.NativeError("NVLS multicast requested but this box exposes no multicast pointer")
+            raise native.NativeError("NVLS multicast requested (--nvls on) but unavailable on rank %d: %s"
+                                     % (rank, why or "another rank has no multicast pointer"))
+        if rank == 0:
+            import warnings
+            warnings.warn("ddl_b200: NVLS multicast was selected automatically for %d ranks but is unavailable (%s); "
+                          "falling back to peer loads / stores over cudaIpc mappings" % (world, why or "peer rank"),
+                          RuntimeWarning, stacklevel=2)
     return SymmetricMemory(nbytes, rank, world, device)
 
 
@@ -192,9 +204,8 @@ class FusedTransport(SpmdTransport):
         self.worker_mask = 0
         for wr in lay.worker_ranks:
             self.worker_mask |= 1 << wr
-        # per-owned-shard argument blocks.  With gradient bucketing every step is served by two launches:
-        # bucket 0 = conv3..fc3 (ready early in the backward; the engine launches it on its side stream),
-        # bucket 1 = conv1 / conv2 (after the backward).  Every rank launches both, in that order.
+        # per-owned-shard argument blocks.  With gradient bucketing every step is served by three launches per owned
+        # shard, in the same order on every rank (see bucket_vars below).
         spec = params.spec
         self.bucketed = bool(cfg.overlap_push and cfg.mode == "sync" and spec.kind == "cnn")
         self.engine_overlap = False
@@ -208,7 +219,7 @@ class FusedTransport(SpmdTransport):
             a.m = self.m.data_ptr() if self.m is not None else None
             a.v = self.v.data_ptr() if self.v is not None else None
             a.st = self.st.data_ptr()
-            a.done_counter = self.scratch[4 * bucket:].data_ptr()
+            a.done_counter = self.scratch[16 + bucket:].data_ptr()
             a.worker_mask = a.dest_mask = self.worker_mask
             a.lr, a.a, a.b, a.eps = cfg.lr, aa, bb, eps
             a.gscale = self.gscale if cfg.mode == "sync" else 1.0
@@ -244,20 +255,27 @@ class FusedTransport(SpmdTransport):
                     merged.append((b, e))
             return merged
 
-        early_vars, late_vars = list(range(4, spec.num_vars)), [0, 1, 2, 3]
+        # buckets in launch order: FC layers (60% of the bytes, complete right after the FC backward), conv3 / conv4
+        # (complete after conv3's dgrad), conv1 / conv2 (after the backward).  The engine launches the first two on its
+        # side stream in the middle of the backward; step() launches the last one.
+        bucket_vars = [list(range(8, spec.num_vars)), [4, 5, 6, 7], [0, 1, 2, 3]]
+        nbk = len(bucket_vars)
         self.sync_args: List[native.SyncArgs] = []        # launched by step()
-        self.early_args: List[native.SyncArgs] = []       # bucket 0 (engine side stream, or step() without engine)
+        self.early_args: List[native.SyncArgs] = []       # overlapped buckets (engine side stream, or step() without engine)
         ranges = [self.plan.shard_range[r] for r in lay.my_shards] or [(0, 0)]
-        for (b, e) in ranges:
+        if self.bucketed and len(ranges) * (nbk - 1) > 8:
+            self.bucketed = False
+        all_subs = [[bucket_subranges(b, e, vs) for vs in bucket_vars] for (b, e) in ranges] if self.bucketed else []
+        if any(len(x) > native.MAX_SUB for subs in all_subs for x in subs):
+            self.bucketed = False
+        for i, (b, e) in enumerate(ranges):
             if self.bucketed:
-                s0, s1 = bucket_subranges(b, e, early_vars), bucket_subranges(b, e, late_vars)
-                if len(s0) > native.MAX_SUB or len(s1) > native.MAX_SUB:
-                    self.bucketed = False
-            if self.bucketed:
-                self.early_args.append(make_args(b, e, 0, 2, s0))
-                self.sync_args.append(make_args(b, e, 1, 2, s1))
+                for k in range(nbk - 1):
+                    self.early_args.append(make_args(b, e, k, nbk, all_subs[i][k]))
+                self.sync_args.append(make_args(b, e, nbk - 1, nbk, all_subs[i][nbk - 1]))
             else:
                 self.sync_args.append(make_args(b, e, 0, 1, None))
+        self.early_args.sort(key=lambda a: a.bucket)      # every rank launches bucket 0 before bucket 1
         if len(ranges) > 1:                               # single-process multi-shard: one launch per shard is fine
             pass
         # ---- K4: variables whose pull is fused into their first consumer GEMM (fc1 / fc2 weights: each weight

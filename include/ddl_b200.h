@@ -37,6 +37,8 @@ typedef struct DdlStepState {
 
 const char* ddl_last_error(void);
 int ddl_version(void);
+/* kernels launched by this library in this process so far (a launch recorded during stream capture counts once) */
+unsigned long long ddl_launch_count(void);
 int ddl_memcpy_async(void* dst, const void* src, size_t bytes, cudaStream_t s);
 
 /* ---- step state / optimizers (ApplyAdam: mnist_sync/parameter_server.py:21-27; model.py:106) */
@@ -59,6 +61,11 @@ int ddl_conv1_wgrad(const float* x, const float* dy, float* dw, float* db, int B
 /* the same gradients from the POOLED layout: after pool + ReLU backward only the argmax pixel of each 2x2 window is
  * non-zero, so the sum runs over the windows (idx [B,S/2,S/2,C], slots 0..3, 4 = dead) - a quarter of the work */
 int ddl_conv1_wgrad_sparse(const float* x, const float* dy, const uint8_t* idx, float* dw, float* db, int B, int S, int C,
+                           cudaStream_t s);
+/* conv1 weight gradient from the pooled gradient: gp [B, S/2, S/2, C] (ReLU-dead windows already 0), idx the argmax
+ * slots; dw[25][C] += sum over windows of gp * x[argmax pixel + tap offset]; db (nullable) += column sums of gp.
+ * x is read before griddepcontrol.wait: it must not be produced by the kernel launched just before.  S == 28. */
+int ddl_conv1_wgrad_pooled(const float* x, const float* gp, const uint8_t* idx, float* dw, float* db, int B, int S, int C,
                            cudaStream_t s);
 /* (bias +) ReLU + tf.nn.max_pool2d 2x2/2 SAME on NHWC conv sums and its gradient (model.py:31,42,53,64);
  * the backward also accumulates the bias gradient of the producing conv into db (may be NULL). */
@@ -131,12 +138,12 @@ DdlTcPlan* ddl_tc_plan_conv_pool(const float* act, const float* w, const float* 
 DdlTcPlan* ddl_tc_plan_dgrad_unpool(const float* dy, const float* w, const uint8_t* idx, float* dfull, float* dbias,
                                     int N, int H, int W, int UH, int UW, int cout, int cin, int ksize, int ntile,
                                     int cluster);
-/* Fold the weight gradient of the ONE-input-channel layer below (conv1, model.py:24-31) into a dgrad_unpool plan:
- * dw1[k1*k1][cin] += sum over the argmax pixels of the routed gradient of g * x1[pixel + tap offset], x1 [N, UH, UW].
- * Only 1/4 of the un-pooled gradient is non-zero, so this replaces a full pass over it.  store_dfull = 0 also drops
- * the un-pooled gradient tensor itself.  ddl_tc_plan_set_x1 re-points x1 (alternating input buffers). */
-int ddl_tc_plan_unpool_w1grad(DdlTcPlan* pl, const float* x1, float* dw1, int k1, int store_dfull);
-int ddl_tc_plan_set_x1(DdlTcPlan* pl, const float* x1);
+/* conv dgrad + the ReLU half of the pool backward, gradient kept in the POOLED layout: gp[N, H, W, cin] = dgrad value
+ * where idx < 4 (window alive), 0 where the window is ReLU-dead; dbias += column sums.  Used for conv2's dgrad: conv1
+ * (model.py:24-31) has no data gradient, and its weight gradient (ddl_conv1_wgrad_pooled) needs only value + argmax
+ * slot per window - the un-pooled plane (4x the bytes, 75% zeros) is never materialised. */
+DdlTcPlan* ddl_tc_plan_dgrad_poolgrad(const float* dy, const float* w, const uint8_t* idx, float* gp, float* dbias,
+                                      int N, int H, int W, int cout, int cin, int ksize, int ntile, int cluster);
 /* host-only planning helpers (no device needed; used by the CPU tests): pixel box of a plan, (N tile, cluster) choice
  * of the staged conv plans and of the FC plans */
 int ddl_plan_choose_box(int N, int H, int W, int max_rows, int row_mult, int even_windows, int* box3);
@@ -255,9 +262,10 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
  * stream beside the convolutions (the first reader of the step state is fc1's dropout); the caller must then NOT
  * advance the state before the step. */
 int ddl_engine_set_advance(DdlEngine* e, float lr, float b1, float b2, int advance_opt);
-/* Backward-overlapped push: the engine launches ddl_sync_push_update_pull for these argument blocks on its
- * side stream as soon as the gradients of conv3..fc3 (98% of the bytes) are complete, while the main stream
- * still runs the conv2 / conv1 backward.  The caller launches the remaining bucket after the step. */
+/* Backward-overlapped push: the engine launches ddl_sync_push_update_pull for these argument blocks on its side
+ * stream while the main stream still runs the rest of the backward - blocks with bucket == 0 (the FC layers, 60% of
+ * the bytes) right after fc1's dgrad, blocks with bucket == 1 (conv3 / conv4) after conv3's dgrad.  The caller
+ * launches the last bucket (conv1 / conv2) after the step.  nargs <= 8. */
 int ddl_engine_set_overlap(DdlEngine* e, const DdlComm* c, const DdlSyncArgs* args, int nargs, int kind);
 /* sess.run(self.accuracy, keep_prob=1) (mnist_sync/worker.py:72) over n rows */
 int ddl_engine_eval(DdlEngine* e, const float* x, const int* y, int n, unsigned* correct, float* logits_out,

@@ -35,7 +35,7 @@ def ref_conv(x_nhwc, w_hwio):
 
 def test_native_library_loaded_and_blackwell():
     from ddl_b200.ops import native
-    assert native.lib().ddl_version() == 100
+    assert native.lib().ddl_version() >= 200
     assert torch.cuda.get_device_capability()[0] == 10, "these kernels are sm_100a only"
 
 
@@ -183,10 +183,10 @@ def test_tc_conv_dgrad_unpool_fused(H, UH, Cin, Cout, B, ntile, cluster):
     assert none is None and torch.equal(got2, got)
 
 
-@pytest.mark.parametrize("B,Cin,ntile,cluster,store", [(100, 32, 32, 1, True), (100, 32, 32, 1, False), (37, 64, 64, 1, True),
-                                                       (100, 32, 32, 2, True), (50, 64, 32, 1, True)])
-def test_tc_dgrad_unpool_with_first_layer_wgrad(B, Cin, ntile, cluster, store):
-    """conv2 dgrad + pool1 backward + conv1's weight AND bias gradient in one kernel, against conv1_wgrad."""
+@pytest.mark.parametrize("B,Cin,ntile,cluster", [(100, 32, 32, 1), (37, 64, 64, 1), (100, 32, 32, 2), (50, 64, 32, 1)])
+def test_tc_dgrad_poolgrad_and_pooled_first_layer_wgrad(B, Cin, ntile, cluster):
+    """conv2's dgrad with the gradient kept in the pooled layout (ReLU-dead windows zeroed, bias gradient summed), then
+    conv1's weight gradient from (pooled gradient, argmax slot): against the un-pool + dense-wgrad kernels and torch."""
     from ddl_b200.ops import functional as K
     torch.manual_seed(13)
     H, UH, Cout = 14, 28, 64
@@ -197,12 +197,17 @@ def test_tc_dgrad_unpool_with_first_layer_wgrad(B, Cin, ntile, cluster, store):
     _, idx = K.bias_relu_maxpool(below)
     want, want_db = K.conv5x5_dgrad_unpool(dy, w, idx, UH, UH, ntile=ntile, cluster=cluster)
     want_dw1, want_db1 = K.conv1_wgrad(x1, want)
-    got, db, dw1 = K.conv5x5_dgrad_unpool(dy, w, idx, UH, UH, ntile=ntile, cluster=cluster, x1=x1, store_dfull=store)
-    assert (got is None) == (not store)
-    if store:
-        assert torch.equal(got, want)
+    gp, db = K.conv5x5_dgrad_poolgrad(dy, w, idx, ntile=ntile, cluster=cluster)
+    assert gp.shape == (B, H, H, Cin)
+    # the pooled gradient is the un-pooled one summed over each window (one non-zero per window at most)
+    assert torch.equal(gp, want.view(B, H, 2, H, 2, Cin).sum(dim=(2, 4)))
+    assert torch.equal(gp == 0, (idx == 4) | (gp == 0))
     assert rel_err(db, want_db) < 1e-3 and rel_err(db, want_db1) < 1e-3
-    assert dw1.shape == want_dw1.shape and rel_err(dw1, want_dw1) < 1e-3
+    dw1, db1 = K.conv1_wgrad_pooled(x1, gp, idx)
+    assert dw1.shape == want_dw1.shape and rel_err(dw1, want_dw1) < 1e-4
+    assert rel_err(db1, want_db1) < 1e-4
+    dw1b, none = K.conv1_wgrad_pooled(x1, gp, idx, want_db=False)
+    assert none is None and rel_err(dw1b, want_dw1) < 1e-4
     # and against torch: dW1 = conv weight gradient of a 1-channel conv
     xr = x1.double().unsqueeze(1).requires_grad_(False)
     wt = torch.zeros(Cin, 1, 5, 5, device=dev(), dtype=torch.double, requires_grad=True)
