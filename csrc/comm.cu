@@ -43,6 +43,21 @@ DDL_DEVICE float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const f
 DDL_DEVICE void pad_signal(const DdlComm& c, uint32_t base, uint32_t epoch) {
   if ((int)threadIdx.x < c.world) st_release_sys(c.pads[threadIdx.x] + base + c.rank, epoch);
 }
+// Same signal without the release: a st.release.sys costs a MEMBAR.SYS (~2 us at the head of a kernel, measured with
+// tools/sync_phase.py).  Two uses, both already ordered by other means:
+//  * barrier A - what the signal publishes (this rank's gradients, and "I am done reading my parameters") was written
+//    by EARLIER kernels of this stream; a kernel boundary completes and flushes them to L2, the point of coherence a
+//    peer's NVLink access reads, before this kernel's first instruction;
+//  * barrier B - the caller is the single thread that has just executed the fences that order this grid's stores.
+DDL_DEVICE void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+DDL_DEVICE void pad_signal_relaxed(const DdlComm& c, uint32_t base, uint32_t epoch) {
+  if ((int)threadIdx.x < c.world) st_relaxed_sys(c.pads[threadIdx.x] + base + c.rank, epoch);
+}
+// signal rows of the sync buckets: one row of DDL_MAX_PEERS slots per bucket, so buckets never see each other's epochs
+// and their kernels need no ordering among themselves
+DDL_DEVICE uint32_t sync_pad_base(int bucket) { return (uint32_t)(DDL_PAD_SYNC + DDL_MAX_PEERS * bucket); }
 DDL_DEVICE void pad_wait(const DdlComm& c, uint32_t base, uint32_t epoch) {
   if ((int)threadIdx.x < c.world) {
     const uint32_t* slot = c.pads[c.rank] + base + threadIdx.x;
@@ -111,43 +126,66 @@ __global__ void __launch_bounds__(kCommThreads)
 sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int stamps_on, const int skip_a) {
   pdl_enter();
   __shared__ uint32_t s_last;
+#ifdef DDL_TC_LAB
   const bool cst = stamps_on && blockIdx.x == 0 && threadIdx.x == 0 && a.bucket == stamps_on - 1;
+#else
+  const bool cst = false;                          // phase stamps exist only in the lab build (ops/build.py --lab)
+#endif
   DDL_CSTAMP(0);
   const uint32_t t = a.st->t;                       // same on every rank: all ranks advance together
   const uint32_t nb = a.nbuckets > 1 ? (uint32_t)a.nbuckets : 1u;
   const uint32_t epochA = 2u * nb * t + 2u * (uint32_t)a.bucket + 1u, epochB = epochA + 1u;
-  // ---- barrier A: my gradients are complete (previous kernels on this stream) -> tell everyone.
-  // The release store is the only fence needed (the explicit fence.sys in front of it cost a second ~4 us
-  // MEMBAR.SYS, tools/sync_phase.py).  A single rank has nobody to wait for: no signals, no system fences.
+  const uint32_t pbase = sync_pad_base(a.bucket);
+  // ---- barrier A: my gradients are complete (previous kernels on this stream) -> tell everyone (see
+  // pad_signal_relaxed).  A single rank has nobody to wait for: no signals, no system fences.
   const bool solo = c.world == 1;
   float* myp = c.params[c.rank];
   const int nsub = a.nsub > 0 ? a.nsub : 1;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  if (!solo && !skip_a) {                           // skip_a: sync_wait_kernel (previous launch on this stream) did it
-    if (blockIdx.x == 0) pad_signal(c, 0, epochA);
-    DDL_CSTAMP(1);
-    // while the signals travel: pull this thread's first optimizer-state lines (local HBM, cold after a full step of
-    // other traffic) into L2, so the loads behind the barrier hit
-    {
-      const int64_t rb0 = a.nsub > 0 ? a.sub_begin[0] : a.begin, re0 = a.nsub > 0 ? a.sub_end[0] : a.end;
-      const int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-      if (q < (re0 - rb0) / 4 && (threadIdx.x & 7) == 0) {           // one prefetch per 128-byte line
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(myp + rb0 + q * 4));
-        if (KIND >= 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.m + rb0 + q * 4));
-        if (KIND == 2) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.v + rb0 + q * 4));
-      }
+  // One flat index space over all sub-ranges of the bucket (float4 units): a thread's trips are spread over the whole
+  // bucket, not restarted per sub-range - a bucket of four small variables is ONE NVLink round trip, not four
+  // dependent ones.
+  int64_t n4 = 0;
+  for (int sr = 0; sr < nsub; ++sr) n4 += ((a.nsub > 0 ? a.sub_end[sr] : a.end) - (a.nsub > 0 ? a.sub_begin[sr] : a.begin)) / 4;
+  auto elem = [&](int64_t q) -> int64_t {          // arena element index of flat float4 index q (q < n4)
+    if (a.nsub <= 0) return a.begin + q * 4;
+    int64_t i = a.sub_begin[0] + q * 4;
+#pragma unroll 1
+    for (int sr = 0; sr < a.nsub; ++sr) {
+      const int64_t len = (a.sub_end[sr] - a.sub_begin[sr]) / 4;
+      if (q < len) { i = a.sub_begin[sr] + q * 4; break; }
+      q -= len;
     }
-    pad_wait(c, 0, epochA);                         // every block polls its own (local) pad
+    return i;
+  };
+  if (!solo && !skip_a) {                           // skip_a: sync_wait_kernel (previous launch on this stream) did it
+    if (blockIdx.x == 0) pad_signal_relaxed(c, pbase, epochA);
+    DDL_CSTAMP(1);
+    pad_wait(c, pbase, epochA);                     // every block polls its own (local) pad
     __syncthreads();
   }
   DDL_CSTAMP(2);
 
   constexpr int WCH = (U == 1) ? DDL_MAX_PEERS : 4;  // peers loaded per batch: WCH * U float4 in flight
   const float step = (KIND == 2) ? a.st->lr_t : a.lr;
-  for (int sr = 0; sr < nsub; ++sr) {
-  const int64_t rb = a.nsub > 0 ? a.sub_begin[sr] : a.begin, re = a.nsub > 0 ? a.sub_end[sr] : a.end;
-  const int64_t n4 = (re - rb) / 4;
   for (int64_t q0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * U) {
+    int64_t ei[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t q = q0 + u * stride;
+      ei[u] = elem(q < n4 ? q : q0);
+    }
+    // optimizer state first: local HBM loads that overlap the NVLink round trip of the gradient loads below (and all U
+    // chunks before the first store: m / v / p may alias for the compiler)
+    float4 pv[U], mv[U], vv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = ei[u];
+      pv[u] = *reinterpret_cast<const float4*>(myp + i);
+      mv[u] = vv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (KIND >= 1) mv[u] = *reinterpret_cast<const float4*>(a.m + i);
+      if (KIND == 2) vv[u] = *reinterpret_cast<const float4*>(a.v + i);
+    }
     float4 g[U];
     if (c.mc_grads != nullptr) {
       // NVLS: the switch sums this offset of every rank's gradient arena (ranks that are not workers hold
@@ -156,7 +194,7 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
       for (int u = 0; u < U; ++u) {
         const int64_t q = q0 + u * stride;
         g[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (q < n4) g[u] = multimem_ld_reduce_add_v4(c.mc_grads + rb + q * 4);
+        if (q < n4) g[u] = multimem_ld_reduce_add_v4(c.mc_grads + ei[u]);
       }
     } else {
       // all peer loads of a batch first, then a fixed-order sum (ascending rank): loads overlap instead of
@@ -173,7 +211,7 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
           for (int u = 0; u < U; ++u) {
             const int64_t q = q0 + u * stride;
             x[wi][u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (on && q < n4) x[wi][u] = ldcg4(c.grads[w] + rb + q * 4);
+            if (on && q < n4) x[wi][u] = ldcg4(c.grads[w] + ei[u]);
           }
         }
 #pragma unroll
@@ -185,22 +223,11 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
         }
       }
     }
-    // optimizer state of all U chunks is loaded before the first store (m / v / p may alias for the compiler)
-    float4 pv[U], mv[U], vv[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int64_t q = q0 + u * stride;
-      const int64_t i = rb + (q < n4 ? q : q0) * 4;
-      pv[u] = *reinterpret_cast<const float4*>(myp + i);
-      mv[u] = vv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (KIND >= 1) mv[u] = *reinterpret_cast<const float4*>(a.m + i);
-      if (KIND == 2) vv[u] = *reinterpret_cast<const float4*>(a.v + i);
-    }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t q = q0 + u * stride;
       if (q >= n4) continue;
-      const int64_t i = rb + q * 4;
+      const int64_t i = ei[u];
       float4 gs = g[u];
       gs.x *= a.gscale; gs.y *= a.gscale; gs.z *= a.gscale; gs.w *= a.gscale;
       const float4 pn = opt_math<KIND>(pv[u], gs, mv[u], vv[u], step, a.a, a.b, a.eps);
@@ -223,7 +250,6 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
       }
     }
   }
-  }
   // ---- barrier B: last block to finish publishes "my range is delivered" and waits for the others.
   // One fence per block, not per thread: bar.sync makes the block's stores observed by thread 0, whose
   // (cumulative) fence then orders them before the counter bump - the cooperative-groups grid-sync idiom.
@@ -240,14 +266,16 @@ sync_push_update_pull_kernel(const DdlComm c, const DdlSyncArgs a, const int sta
   }
   __syncthreads();
   if (s_last) {
-    // Every block's fence + counter bump has been observed by this block's thread 0 through the (relaxed) atomicAdd;
-    // the fence below makes that observation an acquire (fence-fence synchronisation with the other blocks' fences),
-    // bar.sync hands it to the signalling threads, and their release stores order everything (cumulatively) before
-    // the "delivered" signal.
-    if (threadIdx.x == 0) { *a.done_counter = 0; __threadfence_system(); }
-    __syncthreads();
-    pad_signal(c, 0, epochB);
-    pad_wait(c, 0, epochB);
+    // Every block executed fence.sys (its remote stores are performed system-wide) and then bumped the counter; thread 0
+    // of this block saw the last bump.  A gpu-scope fence turns that relaxed observation into an acquire (it pairs with
+    // the other blocks' fences), and the same thread then issues the "delivered" signals - fence, then flag, from one
+    // thread: the message-passing pattern without a second MEMBAR.SYS (1.9 us, tools/sync_phase.py).
+    if (threadIdx.x == 0) {
+      *a.done_counter = 0;
+      __threadfence();
+      for (int r = 0; r < c.world; ++r) st_relaxed_sys(c.pads[r] + pbase + c.rank, epochB);
+    }
+    pad_wait(c, pbase, epochB);
   }
   DDL_CSTAMP(7);
 }
@@ -260,14 +288,16 @@ __global__ void __launch_bounds__(32) sync_wait_kernel(const DdlComm c, const Dd
   pdl_enter();
   const uint32_t nb = a.nbuckets > 1 ? (uint32_t)a.nbuckets : 1u;
   const uint32_t epochA = 2u * nb * a.st->t + 2u * (uint32_t)a.bucket + 1u;
-  pad_signal(c, 0, epochA);
-  pad_wait(c, 0, epochA);
+  pad_signal_relaxed(c, sync_pad_base(a.bucket), epochA);
+  pad_wait(c, sync_pad_base(a.bucket), epochA);
 }
 
 // ------------------------------------------------------------------------------------------------
 // K2 (async): worker pushes its whole gradient arena to the owners with remote atomics.
 // direct_sgd: params[owner][i] += -lr * g[i]  (Hogwild, no owner-side work at all);
-// otherwise:  accum[owner][i]  += g[i]        (owner applies Adam / momentum in ddl_async_apply).
+// otherwise:  accum[owner][slot][i] += g[i], slot = this worker's index: every worker has its own accumulator plane on
+//             every owner, so the owner can apply ONE optimizer step PER PUSH (ddl_async_apply), as the reference's
+//             PS does (mnist_async/parameter_server.py:55-69), instead of one step on the sum of whatever has landed.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kCommThreads)
 async_push_kernel(const DdlComm c, const DdlAsyncArgs a) {
@@ -276,7 +306,7 @@ async_push_kernel(const DdlComm c, const DdlAsyncArgs a) {
   const float* g = c.grads[c.rank];
   for (int o = 0; o < a.num_shards; ++o) {
     const int owner = a.owner_rank[o];
-    float* dst = a.direct_sgd ? c.params[owner] : c.accum[owner];
+    float* dst = a.direct_sgd ? c.params[owner] : c.accum[owner] + (int64_t)a.slot * a.slot_stride;
     const float scale = a.direct_sgd ? -a.lr : 1.f;
     const int64_t b = a.shard_begin[o], n4 = (a.shard_end[o] - b) / 4;
     for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
@@ -296,53 +326,99 @@ async_push_kernel(const DdlComm c, const DdlAsyncArgs a) {
   if (s_last) {
     if (threadIdx.x == 0) { *a.done_counter = 0; __threadfence_system(); }
     __syncthreads();
-    // one release-ordered counter bump per owner: "a complete push has landed"
+    // one release-ordered counter bump per owner: "a complete push of worker `slot` has landed"
     if ((int)threadIdx.x < a.num_shards) {
       const int owner = a.owner_rank[threadIdx.x];
       const uint32_t seen = ld_acquire_sys(c.pads[owner] + DDL_PAD_VERSION);
+      atom_add_release_sys(c.pads[owner] + DDL_PAD_PUSHES_W + a.slot, 1u);
       atom_add_release_sys(c.pads[owner] + DDL_PAD_PUSHES, 1u);
-      // staleness of this push = owner version now - version observed at our last pull
+      // staleness of this push = optimizer steps the owner has taken since our last pull
       const uint32_t stale = seen - a.pulled_version[threadIdx.x];
       atomicAdd(&a.stale_hist[stale < DDL_STALE_BINS - 1 ? stale : DDL_STALE_BINS - 1], 1u);
     }
   }
 }
 
-// owner: 1 thread decides whether pushes are pending and advances the shard's step state
-__global__ void async_snapshot_kernel(const DdlComm c, DdlStepState* st, uint32_t* applied, uint32_t* pending,
+// owner, 1 thread: which workers have pushes pending, how many optimizer steps that makes, and the Adam step size of
+// each.  Parity mode: one step per worker with a pending push, in worker order (a worker that pushed twice since the
+// last apply has both gradients summed in its plane - counted in `folded`).  fold mode: one step on the sum of all.
+__global__ void async_snapshot_kernel(const DdlComm c, DdlStepState* st, DdlAsyncState* as, int nworkers, int fold,
                                       float lr, float b1, float b2) {
   pdl_enter();
   if (threadIdx.x == 0 && blockIdx.x == 0) {
-    const uint32_t pushes = ld_acquire_sys(c.pads[c.rank] + DDL_PAD_PUSHES);
-    const uint32_t n = pushes - *applied;
-    *pending = n;
-    if (n) {
-      *applied = pushes;
-      const uint32_t t = st->t + 1;
-      st->t = t;
-      st->lr_t = (float)((double)lr * sqrt(1.0 - pow((double)b2, (double)t)) / (1.0 - pow((double)b1, (double)t)));
+    uint32_t mask = 0, nsteps = 0;
+    uint32_t t = st->t;
+    for (int w = 0; w < nworkers; ++w) {
+      const uint32_t cnt = ld_acquire_sys(c.pads[c.rank] + DDL_PAD_PUSHES_W + w);
+      const uint32_t n = cnt - as->applied[w];
+      if (n) {
+        as->applied[w] = cnt;
+        mask |= 1u << w;
+        as->folded += n - 1;
+        if (!fold || nsteps == 0) {
+          ++t;
+          as->lr_t[nsteps] = (float)((double)lr * sqrt(1.0 - pow((double)b2, (double)t)) / (1.0 - pow((double)b1, (double)t)));
+          ++nsteps;
+        } else {
+          as->folded += 1;                       // fold mode: this worker's push shares the step of an earlier one
+        }
+      }
     }
+    as->mask = mask;
+    as->nsteps = nsteps;
+    if (nsteps) { st->t = t; st->lr_t = as->lr_t[nsteps - 1]; }
   }
 }
 
 template <int KIND>
 __global__ void __launch_bounds__(kCommThreads)
-async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const uint32_t* pending) {
+async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const DdlAsyncState* as, int nworkers, int64_t slot_stride, int fold) {
   pdl_enter();
   __shared__ uint32_t s_last;
-  if (*pending == 0) return;
-  const float step = (KIND == 2) ? a.st->lr_t : a.lr;
+  const uint32_t mask = as->mask;
+  if (mask == 0) return;
   float* myp = c.params[c.rank];
   float* acc = c.accum[c.rank];
   const int64_t n4 = (a.end - a.begin) / 4;
   for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = a.begin + q * 4;
-    float4 g;                                        // consume exactly once, even against in-flight adds
-    g.x = atomicExch(acc + i, 0.f); g.y = atomicExch(acc + i + 1, 0.f);
-    g.z = atomicExch(acc + i + 2, 0.f); g.w = atomicExch(acc + i + 3, 0.f);
-    g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
-    const float4 pn = opt_apply<KIND>(*reinterpret_cast<float4*>(myp + i), g, a.m, a.v, i, step, a.a, a.b, a.eps);
-    *reinterpret_cast<float4*>(myp + i) = pn;
+    float4 pv = *reinterpret_cast<float4*>(myp + i);
+    float4 mv = make_float4(0.f, 0.f, 0.f, 0.f), vv = mv;
+    if (KIND >= 1) mv = *reinterpret_cast<float4*>(a.m + i);
+    if (KIND == 2) vv = *reinterpret_cast<float4*>(a.v + i);
+    // every pending plane is consumed exactly once (atomicExch), even against adds still in flight for a LATER push;
+    // all exchanges are issued before the first optimizer step
+    float4 g[DDL_MAX_PEERS];
+#pragma unroll
+    for (int w = 0; w < DDL_MAX_PEERS; ++w) {
+      g[w] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (w < nworkers && ((mask >> w) & 1u)) {
+        float* pl = acc + (int64_t)w * slot_stride + i;
+        g[w].x = atomicExch(pl, 0.f); g[w].y = atomicExch(pl + 1, 0.f);
+        g[w].z = atomicExch(pl + 2, 0.f); g[w].w = atomicExch(pl + 3, 0.f);
+      }
+    }
+    if (fold) {
+      float4 gs = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int w = 0; w < DDL_MAX_PEERS; ++w) { gs.x += g[w].x; gs.y += g[w].y; gs.z += g[w].z; gs.w += g[w].w; }
+      gs.x *= a.gscale; gs.y *= a.gscale; gs.z *= a.gscale; gs.w *= a.gscale;
+      pv = opt_math<KIND>(pv, gs, mv, vv, KIND == 2 ? as->lr_t[0] : a.lr, a.a, a.b, a.eps);
+    } else {
+      int k = 0;
+#pragma unroll
+      for (int w = 0; w < DDL_MAX_PEERS; ++w) {
+        if (w < nworkers && ((mask >> w) & 1u)) {
+          float4 gs = g[w];
+          gs.x *= a.gscale; gs.y *= a.gscale; gs.z *= a.gscale; gs.w *= a.gscale;
+          pv = opt_math<KIND>(pv, gs, mv, vv, KIND == 2 ? as->lr_t[k] : a.lr, a.a, a.b, a.eps);
+          ++k;
+        }
+      }
+    }
+    if (KIND >= 1) *reinterpret_cast<float4*>(a.m + i) = mv;
+    if (KIND == 2) *reinterpret_cast<float4*>(a.v + i) = vv;
+    *reinterpret_cast<float4*>(myp + i) = pv;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -353,7 +429,7 @@ async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const uint32_t* pending
   if (s_last && threadIdx.x == 0) {
     *a.done_counter = 0;
     __threadfence_system();
-    atom_add_release_sys(c.pads[c.rank] + DDL_PAD_VERSION, 1u);
+    atom_add_release_sys(c.pads[c.rank] + DDL_PAD_VERSION, as->nsteps);
   }
 }
 
@@ -391,6 +467,68 @@ __global__ void device_barrier_kernel(const DdlComm c, uint32_t* epoch_counter) 
   pad_wait(c, DDL_PAD_BARRIER, e);
 }
 
+// NVLink probe (tools/p2p_probe.py): one thread issues `iters` DEPENDENT 4-byte loads from `src` (a peer-mapped or local
+// pointer; the value loaded selects the next address, so no two are in flight), sleeping `idle_ns` before each one.
+// out[0] = total ns spent in the loads, out[1] = ns of the first load, out[2] = max, out[3] = checksum.
+__global__ void p2p_latency_kernel(const uint32_t* src, int words, int iters, unsigned idle_ns, unsigned long long* out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  unsigned long long total = 0, first = 0, worst = 0;
+  uint32_t idx = 0, sum = 0;
+  for (int i = 0; i < iters; ++i) {
+    if (idle_ns) __nanosleep(idle_ns);
+    const unsigned long long t0 = ddl_globaltimer();
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(src + idx) : "memory");
+    idx = (idx + 97u * 32u + (v & 1u)) % (uint32_t)words;       // depends on v: the next load cannot start early
+    sum += v;
+    const unsigned long long dt = ddl_globaltimer() - t0;
+    total += dt;
+    if (i == 0) first = dt;
+    if (dt > worst) worst = dt;
+  }
+  out[0] = total; out[1] = first; out[2] = worst; out[3] = sum;
+}
+
+// one thread: `iters` 4-byte stores to `dst`, each followed by fence.sys (returns once the store is performed at its
+// destination): the store + acknowledgement round trip that a "delivered" signal has to wait for
+__global__ void p2p_store_fence_kernel(uint32_t* dst, int words, int iters, unsigned idle_ns, unsigned long long* out) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  unsigned long long total = 0, first = 0, worst = 0;
+  for (int i = 0; i < iters; ++i) {
+    if (idle_ns) __nanosleep(idle_ns);
+    const unsigned long long t0 = ddl_globaltimer();
+    st_relaxed_sys(dst + (i * 97 * 32) % words, (uint32_t)i);
+    __threadfence_system();
+    const unsigned long long dt = ddl_globaltimer() - t0;
+    total += dt;
+    if (i == 0) first = dt;
+    if (dt > worst) worst = dt;
+  }
+  out[0] = total; out[1] = first; out[2] = worst; out[3] = 0;
+}
+
+// probe: `gridDim.x` blocks, two threads each, poll a flag with ld.acquire.sys for `ns` nanoseconds - what the blocks of a
+// sync kernel do while they wait for a barrier; run next to the latency probes to see what the polling costs others
+__global__ void p2p_spin_kernel(const uint32_t* flag, unsigned long long ns, unsigned long long* out) {
+  if (threadIdx.x >= 2) return;
+  const unsigned long long t0 = ddl_globaltimer();
+  unsigned long long polls = 0;
+  while (ddl_globaltimer() - t0 < ns) { if (ld_acquire_sys(flag + threadIdx.x) == 0xffffffffu) break; ++polls; }
+  if (blockIdx.x == 0 && threadIdx.x == 0) out[0] = polls;
+}
+
+// bandwidth probe: grid-stride float4 copy dst <- src (either may be a peer pointer), 4 loads in flight per thread
+__global__ void __launch_bounds__(256) p2p_copy_kernel(float4* __restrict__ dst, const float4* __restrict__ src, int64_t n4) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q0 < n4; q0 += 4 * stride) {
+    float4 x[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) if (q0 + u * stride < n4) x[u] = __ldcg(src + q0 + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) if (q0 + u * stride < n4) __stcg(dst + q0 + u * stride, x[u]);
+  }
+}
+
 int comm_grid(int64_t elems) {
   // ~2 float4 per thread: the update is a latency-bound stream (7 arena-sized passes), so it wants many threads in
   // flight rather than a long grid-stride loop
@@ -408,6 +546,27 @@ extern "C" {
 int ddl_comm_stamps(int on, unsigned long long* out, int n) {
   g_cstamps_host = on;
   if (out && n > 0) DDL_CHECK_CUDA(cudaMemcpyFromSymbol(out, g_cstamps, sizeof(unsigned long long) * (n > 16 ? 16 : n)));
+  return 0;
+}
+
+/* NVLink probes (tools/p2p_probe.py -> profiles/nvlink_peak.json); out4 is device memory (4 x uint64) */
+int ddl_p2p_latency(const void* src, int words, int iters, unsigned idle_ns, int store_fence, unsigned long long* out4,
+                    cudaStream_t s) {
+  DDL_REQUIRE(words >= 4096 && iters >= 1, "ddl_p2p_latency: need >= 4096 words and >= 1 iteration");
+  if (store_fence) p2p_store_fence_kernel<<<1, 32, 0, s>>>((uint32_t*)src, words, iters, idle_ns, out4);
+  else p2p_latency_kernel<<<1, 32, 0, s>>>((const uint32_t*)src, words, iters, idle_ns, out4);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+int ddl_p2p_spin(const void* flag, int blocks, unsigned long long ns, unsigned long long* out1, cudaStream_t s) {
+  p2p_spin_kernel<<<blocks, 32, 0, s>>>((const uint32_t*)flag, ns, out1);
+  DDL_LAUNCH_CHECK();
+  return 0;
+}
+int ddl_p2p_copy(void* dst, const void* src, int64_t bytes, int blocks, cudaStream_t s) {
+  DDL_REQUIRE(bytes % 16 == 0 && blocks >= 1, "ddl_p2p_copy: bytes %% 16 == 0, blocks >= 1");
+  p2p_copy_kernel<<<blocks, 256, 0, s>>>((float4*)dst, (const float4*)src, bytes / 16);
+  DDL_LAUNCH_CHECK();
   return 0;
 }
 
@@ -484,13 +643,14 @@ int ddl_async_push(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s) {
   return 0;
 }
 
-int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, uint32_t* applied, uint32_t* pending,
-                    float b1, float b2, cudaStream_t s) {
-  DDL_LAUNCH(async_snapshot_kernel, 1, 32, 0, s, *c, a->st, applied, pending, a->lr, b1, b2);
+int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, DdlAsyncState* state, int nworkers,
+                    int64_t slot_stride, int fold, float b1, float b2, cudaStream_t s) {
+  DDL_REQUIRE(nworkers >= 1 && nworkers <= DDL_MAX_PEERS, "ddl_async_apply: %d workers out of range", nworkers);
+  DDL_LAUNCH(async_snapshot_kernel, 1, 32, 0, s, *c, a->st, state, nworkers, fold, a->lr, b1, b2);
   const int grid = comm_grid(a->end - a->begin);
-  if (kind == 0) DDL_LAUNCH(async_apply_kernel<0>, grid, kCommThreads, 0, s, *c, *a, pending);
-  else if (kind == 1) DDL_LAUNCH(async_apply_kernel<1>, grid, kCommThreads, 0, s, *c, *a, pending);
-  else DDL_LAUNCH(async_apply_kernel<2>, grid, kCommThreads, 0, s, *c, *a, pending);
+  if (kind == 0) DDL_LAUNCH(async_apply_kernel<0>, grid, kCommThreads, 0, s, *c, *a, (const DdlAsyncState*)state, nworkers, slot_stride, fold);
+  else if (kind == 1) DDL_LAUNCH(async_apply_kernel<1>, grid, kCommThreads, 0, s, *c, *a, (const DdlAsyncState*)state, nworkers, slot_stride, fold);
+  else DDL_LAUNCH(async_apply_kernel<2>, grid, kCommThreads, 0, s, *c, *a, (const DdlAsyncState*)state, nworkers, slot_stride, fold);
   DDL_LAUNCH_CHECK();
   return 0;
 }

@@ -429,9 +429,8 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   // Main stream: the data-gradient chain.  Side stream: every weight-gradient GEMM, forked as soon as its
   // dY exists and joined once before the optimizer.
   cudaStream_t w = e->side;
-  static const bool one_wstream = getenv("DDL_ONE_WGRAD_STREAM") != nullptr;
   // stream of layer l's conv wgrad (l = 3, 2, 1 <-> conv4, conv3, conv2)
-  auto wstream = [&](int l) -> cudaStream_t { return (one_wstream || l == 3) ? w : e->wside[2 - l]; };
+  auto wstream = [&](int l) -> cudaStream_t { return l == 3 ? w : e->wside[2 - l]; };
   int fk = 0;
   auto fork = [&](cudaStream_t to) -> int {
     DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork[fk], s));
@@ -439,10 +438,11 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     ++fk;
     return 0;
   };
-  // Overlapped push buckets (side2 stream, in bucket order on every rank):
-  //   bucket 0 = the FC layers (60% of the bytes): once their weight gradients (stream w) exist and fc1's dgrad - the
-  //              last reader of a weight this bucket updates in place - has run on the main stream;
-  //   bucket 1 = conv3 / conv4: once their weight gradients (wside[0], w) exist and conv3's dgrad has run.
+  // Overlapped push buckets (each has its own signal row, so their kernels need no order among themselves):
+  //   bucket 0 = the FC layers (60% of the bytes), stream side2: once their weight gradients (stream w) exist and fc1's
+  //              dgrad - the last reader of a weight this bucket updates in place - has run on the main stream;
+  //   bucket 1 = conv4, behind its weight gradient on stream w, once conv4's dgrad has run;
+  //   bucket 2 = conv3, behind its weight gradient on wside[0], once conv3's dgrad has run.
   // The bias gradients come from main-stream kernels that have run by then.  The caller launches the last bucket
   // (conv1 / conv2) after the step.
   auto launch_bucket = [&](int bucket, cudaStream_t bs) -> int {
@@ -455,19 +455,16 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fc_w, 0));
     DDL_CHECK_CUDA(cudaEventRecord(e->ev_fc_m, s));
     DDL_CHECK_CUDA(cudaStreamWaitEvent(e->side2, e->ev_fc_m, 0));
-    return launch_bucket(0, e->side2);
-  };
-  auto launch_overlap = [&](cudaStream_t after_conv3) -> int {
-    // bucket 1 rides the stream of conv3's weight gradient (its last producer) instead of opening one more parallel
-    // branch in the step graph; bucket 0 (side2) is ordered before it so every rank launches the buckets in one order
-    DDL_CHECK_CUDA(cudaEventRecord(e->ev_fork2, e->side2));
-    DDL_CHECK_CUDA(cudaStreamWaitEvent(after_conv3, e->ev_fork2, 0));
-    if (after_conv3 != w) DDL_CHECK_CUDA(cudaStreamWaitEvent(after_conv3, e->ev_w0, 0));
-    DDL_CHECK_CUDA(cudaEventRecord(e->ev_main2, s));
-    DDL_CHECK_CUDA(cudaStreamWaitEvent(after_conv3, e->ev_main2, 0));
-    if (launch_bucket(1, after_conv3)) return -1;
-    DDL_CHECK_CUDA(cudaEventRecord(e->ev_join2, after_conv3));
+    if (launch_bucket(0, e->side2)) return -1;
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_join2, e->side2));
     return 0;
+  };
+  // bucket `bucket` on the stream `ws` of the layer's weight gradient, after the main stream's latest kernel (the
+  // layer's dgrad: the last reader of the weights the bucket updates in place)
+  auto launch_overlap_conv = [&](int bucket, cudaStream_t ws, cudaEvent_t ev) -> int {
+    DDL_CHECK_CUDA(cudaEventRecord(ev, s));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(ws, ev, 0));
+    return launch_bucket(bucket, ws);
   };
   if (fork(w)) return -1;
   if (ddl_tc_plan_run(e->wg_fc[1], w)) return -1;
@@ -488,9 +485,9 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
       cudaStream_t wl = wstream(l);
       if (fork(wl)) return -1;
       if (ddl_tc_plan_run(e->wg_conv[l - 1], wl)) return -1;
-      if (l == 3) DDL_CHECK_CUDA(cudaEventRecord(e->ev_w0, w));
       if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
-      if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
+      if (l == 3 && e->ov_n > 0 && launch_overlap_conv(1, wl, e->ev_fork2)) return -1;
+      if (l == 2 && e->ov_n > 0 && launch_overlap_conv(2, wl, e->ev_main2)) return -1;
     }
   }
   for (int l = unpool ? 0 : 3; l >= 1; --l, v -= 2) {           // conv4, conv3, conv2
@@ -501,9 +498,9 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
     cudaStream_t wl = wstream(l);
     if (fork(wl)) return -1;
     if (ddl_tc_plan_run(e->wg_conv[l - 1], wl)) return -1;
-    if (l == 3) DDL_CHECK_CUDA(cudaEventRecord(e->ev_w0, w));
     if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
-    if (l == 2 && e->ov_n > 0 && launch_overlap(wl)) return -1;
+    if (l == 3 && e->ov_n > 0 && launch_overlap_conv(1, wl, e->ev_fork2)) return -1;
+    if (l == 2 && e->ov_n > 0 && launch_overlap_conv(2, wl, e->ev_main2)) return -1;
   }
   if (!unpool && ddl_maxpool_bwd(e->dpool[0], e->idx[0], e->dfull[0], nullptr, B, e->S[0], e->S[0], e->C[1], s)) return -1;
   if (unpool && e->w1_pooled) {
@@ -516,11 +513,9 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   }
   DDL_CHECK_CUDA(cudaEventRecord(e->ev_join, w));
   DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join, 0));
-  if (!one_wstream) {
-    for (int i = 0; i < 2; ++i) {
-      DDL_CHECK_CUDA(cudaEventRecord(e->ev_wjoin[i], e->wside[i]));
-      DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_wjoin[i], 0));
-    }
+  for (int i = 0; i < 2; ++i) {
+    DDL_CHECK_CUDA(cudaEventRecord(e->ev_wjoin[i], e->wside[i]));
+    DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_wjoin[i], 0));
   }
   if (e->ov_n > 0) DDL_CHECK_CUDA(cudaStreamWaitEvent(s, e->ev_join2, 0));
   return 0;

@@ -17,6 +17,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 CSRC = os.path.join(ROOT, "csrc")
 LIBDIR = os.path.join(ROOT, "ddl_b200", "lib")
 LIB = os.path.join(LIBDIR, "libddl_b200.so")
+LAB_LIB = os.path.join(LIBDIR, "libddl_b200_lab.so")     # same sources + -DDDL_TC_LAB: in-kernel traces / phase stamps / skip switches
+                                                          # used by tools/tc_*.py, wgrad_trace.py, sync_phase.py (DDL_LAB=1)
 OBJDIR = os.path.join(ROOT, "build", "obj")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
@@ -33,25 +35,27 @@ def sources():
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
-def _digest() -> str:
+def _digest(lab: bool = False) -> str:
     h = hashlib.sha256()
     for path in sources() + [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cuh", ".h"))] \
             + [os.path.join(ROOT, "include", "ddl_b200.h")]:
         with open(path, "rb") as f:             # relative names: the stamp must survive a move of the tree
             h.update(os.path.relpath(path, ROOT).encode() + b"\0" + f.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(" ".join(NVCC_FLAGS + (["-DDDL_TC_LAB"] if lab else [])).encode())
     return h.hexdigest()
 
 
-def needs_build() -> bool:
-    stamp = LIB + ".sha256"
-    if not (os.path.exists(LIB) and os.path.exists(stamp)):
+def needs_build(lab: bool = False) -> bool:
+    lib = LAB_LIB if lab else LIB
+    stamp = lib + ".sha256"
+    if not (os.path.exists(lib) and os.path.exists(stamp)):
         return True
-    return open(stamp).read().strip() != _digest()
+    return open(stamp).read().strip() != _digest(lab)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, lab: bool = False) -> str:
+    LIB = LAB_LIB if lab else globals()["LIB"]
+    if not force and not needs_build(lab):
         return LIB
     os.makedirs(LIBDIR, exist_ok=True)
     os.makedirs(OBJDIR, exist_ok=True)
@@ -59,8 +63,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     logs = {}
 
     def compile_one(src):
-        obj = os.path.join(OBJDIR, "%s.%d.o" % (os.path.basename(src)[:-3], os.getpid()))
-        cmd = [exe] + NVCC_FLAGS + ["-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
+        obj = os.path.join(OBJDIR, "%s%s.%d.o" % (os.path.basename(src)[:-3], ".lab" if lab else "", os.getpid()))
+        cmd = [exe] + NVCC_FLAGS + (["-DDDL_TC_LAB"] if lab else []) + ["-I", os.path.join(ROOT, "include"), "-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         logs[src] = r.stdout + r.stderr
         if r.returncode != 0:
@@ -81,9 +85,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         except OSError:
             pass
     with open(LIB + ".sha256.tmp.%d" % os.getpid(), "w") as f:
-        f.write(_digest())
+        f.write(_digest(lab))
     os.replace(LIB + ".sha256.tmp.%d" % os.getpid(), LIB + ".sha256")
-    with open(os.path.join(ROOT, "build", "ptxas.log"), "w") as f:
+    with open(os.path.join(ROOT, "build", "ptxas_lab.log" if lab else "ptxas.log"), "w") as f:
         for src, log in logs.items():
             f.write("==== %s\n%s\n" % (os.path.relpath(src, ROOT), log))
     if verbose:
@@ -93,4 +97,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, lab="--lab" in sys.argv))

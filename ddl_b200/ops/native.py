@@ -18,9 +18,10 @@ MAX_PEERS = 16
 MAX_SKIP = 4
 MAX_SUB = 16
 STALE_BINS = 16
-PAD_SLOTS = 64
+PAD_SLOTS = 256
 PAD_PUSHES = 32
 PAD_VERSION = 33
+PAD_PUSHES_W = 48
 
 
 class StepState(C.Structure):
@@ -54,7 +55,13 @@ class AsyncArgs(C.Structure):
     _fields_ = [("num_shards", C.c_int), ("owner_rank", C.c_int * MAX_PEERS),
                 ("shard_begin", C.c_int64 * MAX_PEERS), ("shard_end", C.c_int64 * MAX_PEERS),
                 ("direct_sgd", C.c_int), ("lr", C.c_float), ("done_counter", C.c_void_p),
-                ("pulled_version", C.c_void_p), ("stale_hist", C.c_void_p)]
+                ("pulled_version", C.c_void_p), ("stale_hist", C.c_void_p),
+                ("slot", C.c_int), ("slot_stride", C.c_int64)]
+
+
+class AsyncState(C.Structure):
+    _fields_ = [("applied", C.c_uint32 * MAX_PEERS), ("mask", C.c_uint32), ("nsteps", C.c_uint32),
+                ("folded", C.c_uint32), ("pad", C.c_uint32), ("lr_t", C.c_float * MAX_PEERS)]
 
 
 class EngineCfg(C.Structure):
@@ -80,10 +87,11 @@ def lib() -> C.CDLL:
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = _build.LIB
-    if _build.needs_build():
+    lab = os.environ.get("DDL_LAB", "") not in ("", "0")      # instrumented build for the tools/ phase and trace scripts
+    path = _build.LAB_LIB if lab else _build.LIB
+    if _build.needs_build(lab):
         try:
-            _build.build()
+            _build.build(lab=lab)
         except Exception as e:                      # no nvcc on the box: a stale .so is an error, not a fallback
             if not os.path.exists(path):
                 raise NativeError("libddl_b200.so is missing and could not be built: %s" % e)
@@ -131,8 +139,11 @@ def lib() -> C.CDLL:
         "ddl_set_device": ([i32], i32),
         "ddl_can_access_peer": ([i32, i32], i32),
         "ddl_sync_push_update_pull": ([C.POINTER(Comm), C.POINTER(SyncArgs), i32, vp], i32),
+        "ddl_p2p_latency": ([vp, i32, i32, u32, i32, vp, vp], i32),
+        "ddl_p2p_copy": ([vp, vp, i64, i32, vp], i32),
+        "ddl_p2p_spin": ([vp, i32, C.c_uint64, vp, vp], i32),
         "ddl_async_push": ([C.POINTER(Comm), C.POINTER(AsyncArgs), vp], i32),
-        "ddl_async_apply": ([C.POINTER(Comm), C.POINTER(SyncArgs), i32, vp, vp, f32, f32, vp], i32),
+        "ddl_async_apply": ([C.POINTER(Comm), C.POINTER(SyncArgs), i32, vp, i32, i64, i32, f32, f32, vp], i32),
         "ddl_pull_allgather": ([C.POINTER(Comm), C.POINTER(AsyncArgs), vp], i32),
         "ddl_device_barrier": ([C.POINTER(Comm), vp, vp], i32),
         "ddl_engine_create": ([C.POINTER(EngineCfg)], vp),

@@ -170,7 +170,9 @@ class FusedTransport(SpmdTransport):
                "grads": _alloc_arena(nbytes, layout.rank, world, device, want_mc),
                "pad": SymmetricMemory(native.PAD_SLOTS * 4, layout.rank, world, device)}
         if cfg.mode == "async":
-            mem["accum"] = SymmetricMemory(nbytes, layout.rank, world, device)
+            # one accumulator plane per worker on every rank (only owned ranges are ever touched): the owner can then
+            # apply one optimizer step per push instead of one step on the sum of whatever has landed
+            mem["accum"] = SymmetricMemory(nbytes * max(1, layout.num_workers), layout.rank, world, device)
         params = Arena(spec, plan, device, mem["params"].tensor())
         grads = Arena(spec, plan, device, mem["grads"].tensor())
         return cls(cfg, layout, params, grads, mem)
@@ -255,15 +257,16 @@ class FusedTransport(SpmdTransport):
                     merged.append((b, e))
             return merged
 
-        # buckets in launch order: FC layers (60% of the bytes, complete right after the FC backward), conv3 / conv4
-        # (complete after conv3's dgrad), conv1 / conv2 (after the backward).  The engine launches the first two on its
-        # side stream in the middle of the backward; step() launches the last one.
-        bucket_vars = [list(range(8, spec.num_vars)), [4, 5, 6, 7], [0, 1, 2, 3]]
+        # buckets: FC layers (60% of the bytes, complete right after the FC backward), conv4, conv3 (each complete once
+        # that layer's dgrad and wgrad have run), conv1 / conv2 (after the backward).  The engine launches the first
+        # three in the middle of the backward, behind the kernels that produce their gradients; step() launches the
+        # last one.  Every bucket has its own signal row, so bucket kernels are independent of each other.
+        bucket_vars = [list(range(8, spec.num_vars)), [6, 7], [4, 5], [0, 1, 2, 3]]
         nbk = len(bucket_vars)
         self.sync_args: List[native.SyncArgs] = []        # launched by step()
         self.early_args: List[native.SyncArgs] = []       # overlapped buckets (engine side stream, or step() without engine)
         ranges = [self.plan.shard_range[r] for r in lay.my_shards] or [(0, 0)]
-        if self.bucketed and len(ranges) * (nbk - 1) > 8:
+        if self.bucketed and (len(ranges) * (nbk - 1) > 8 or spec.num_vars != 14):
             self.bucketed = False
         all_subs = [[bucket_subranges(b, e, vs) for vs in bucket_vars] for (b, e) in ranges] if self.bucketed else []
         if any(len(x) > native.MAX_SUB for subs in all_subs for x in subs):
@@ -307,6 +310,9 @@ class FusedTransport(SpmdTransport):
         aa.done_counter = self.scratch[1:].data_ptr()
         aa.pulled_version = self.pulled_version.data_ptr()
         aa.stale_hist = self.stale_hist.data_ptr()
+        aa.slot = lay.my_worker or 0
+        aa.slot_stride = self.plan.total
+        self.async_state = torch.zeros(C.sizeof(native.AsyncState) // 4, dtype=torch.int32, device=dev)
         self.barrier_epoch = self.scratch[8:]
 
     # ------------------------------------------------------------------------------
@@ -396,8 +402,8 @@ class FusedTransport(SpmdTransport):
             return
         c = self.cfg
         for a in self.sync_args:
-            native.check(self.L.ddl_async_apply(C.byref(self.comm), C.byref(a), self.kind,
-                                                self.scratch[2:].data_ptr(), self.scratch[3:].data_ptr(),
+            native.check(self.L.ddl_async_apply(C.byref(self.comm), C.byref(a), self.kind, self.async_state.data_ptr(),
+                                                self.layout.num_workers, self.plan.total, 1 if c.async_fold else 0,
                                                 c.beta1, c.beta2, self._s()), "ddl_async_apply")
             native.count(2)
 
@@ -448,6 +454,9 @@ class FusedTransport(SpmdTransport):
             pad = self.mem["pad"].tensor(torch.int32).cpu()
             out["pushes_received"] = int(pad[native.PAD_PUSHES])
             out["shard_version"] = int(pad[native.PAD_VERSION])
+            # pushes that shared an optimizer step with another push: a worker that pushed twice between two applies
+            # (its plane holds the sum), or every extra push under --async-fold.  optimizer_steps + folded == pushes.
+            out["folded_pushes"] = int(self.async_state[native.MAX_PEERS + 2].item())
         return out
 
     def opt_state(self):

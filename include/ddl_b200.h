@@ -178,7 +178,9 @@ int ddl_conv5x5_relu_pool_static(const float* x, const float* w, const float* bi
 #define DDL_PAD_BARRIER 16   /* [16,32): host-requested device barrier epochs, one slot per source */
 #define DDL_PAD_PUSHES 32    /* async: complete pushes landed in this owner's accumulator          */
 #define DDL_PAD_VERSION 33   /* async: optimizer applications done by this owner                   */
-#define DDL_PAD_SLOTS 64
+#define DDL_PAD_PUSHES_W 48  /* [48,64): async: complete pushes of worker w landed in this owner's plane w      */
+#define DDL_PAD_SYNC 64      /* [64, 64 + 16*8): sync-bucket barrier epochs, one row of 16 slots per bucket  */
+#define DDL_PAD_SLOTS 256
 
 typedef struct DdlComm {
   int rank, world;
@@ -218,8 +220,25 @@ typedef struct DdlAsyncArgs {
   uint32_t* done_counter;
   uint32_t* pulled_version;        /* [num_shards] owner version seen at the last pull    */
   uint32_t* stale_hist;            /* [DDL_STALE_BINS] staleness histogram of my pushes   */
+  int slot;                        /* my worker index = my accumulator plane on every owner */
+  int64_t slot_stride;             /* elements between planes (the arena size)             */
 } DdlAsyncArgs;
 
+/* owner-side bookkeeping of async mode (device memory, zero-initialised) */
+typedef struct DdlAsyncState {
+  uint32_t applied[DDL_MAX_PEERS]; /* pushes of worker w already consumed                              */
+  uint32_t mask, nsteps;           /* latest apply: workers consumed, optimizer steps taken            */
+  uint32_t folded;                 /* pushes that shared an optimizer step with another push           */
+  uint32_t pad;
+  float lr_t[DDL_MAX_PEERS];       /* TF1-Adam step size of each step of the latest apply              */
+} DdlAsyncState;
+
+/* NVLink probes behind profiles/nvlink_peak.json: dependent-load / store+fence round trips of one thread (out4: 4 x
+ * uint64 device words = total ns, first, max, checksum), a polling kernel and a float4 copy kernel for bandwidth */
+int ddl_p2p_latency(const void* src, int words, int iters, unsigned idle_ns, int store_fence, unsigned long long* out4,
+                    cudaStream_t s);
+int ddl_p2p_spin(const void* flag, int blocks, unsigned long long ns, unsigned long long* out1, cudaStream_t s);
+int ddl_p2p_copy(void* dst, const void* src, int64_t bytes, int blocks, cudaStream_t s);
 int ddl_dev_malloc(void** p, size_t bytes);
 int ddl_dev_free(void* p);
 int ddl_ipc_export(void* p, void* handle64);
@@ -231,8 +250,11 @@ int ddl_can_access_peer(int dev, int peer);
 int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, cudaStream_t s);
 /* K2, async mode (AS/worker.py:36 + AS/ps.py:99-111). */
 int ddl_async_push(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s);
-int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, uint32_t* applied, uint32_t* pending,
-                    float b1, float b2, cudaStream_t s);
+/* Owner side: consume what has landed since the last call.  Default (fold = 0): ONE optimizer step per worker with a
+ * pending push, in worker order, each on that worker's own accumulator plane - mnist_async/parameter_server.py:55-69
+ * applies Adam once per received gradient.  fold = 1: one step on the sum of all pending planes (round-1 behaviour). */
+int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, DdlAsyncState* state, int nworkers,
+                    int64_t slot_stride, int fold, float b1, float b2, cudaStream_t s);
 /* K3 stand-alone (initial pull, async pull, pre-eval refresh). */
 int ddl_pull_allgather(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s);
 int ddl_device_barrier(const DdlComm* c, uint32_t* epoch_counter, cudaStream_t s);
@@ -262,9 +284,9 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
  * stream beside the convolutions (the first reader of the step state is fc1's dropout); the caller must then NOT
  * advance the state before the step. */
 int ddl_engine_set_advance(DdlEngine* e, float lr, float b1, float b2, int advance_opt);
-/* Backward-overlapped push: the engine launches ddl_sync_push_update_pull for these argument blocks on its side
- * stream while the main stream still runs the rest of the backward - blocks with bucket == 0 (the FC layers, 60% of
- * the bytes) right after fc1's dgrad, blocks with bucket == 1 (conv3 / conv4) after conv3's dgrad.  The caller
+/* Backward-overlapped push: the engine launches ddl_sync_push_update_pull for these argument blocks while the main
+ * stream still runs the rest of the backward - blocks with bucket == 0 (the FC layers, 60% of the bytes) right after
+ * fc1's dgrad, bucket == 1 (conv4) after conv4's dgrad and wgrad, bucket == 2 (conv3) after conv3's.  The caller
  * launches the last bucket (conv1 / conv2) after the step.  nargs <= 8. */
 int ddl_engine_set_overlap(DdlEngine* e, const DdlComm* c, const DdlSyncArgs* args, int nargs, int kind);
 /* sess.run(self.accuracy, keep_prob=1) (mnist_sync/worker.py:72) over n rows */

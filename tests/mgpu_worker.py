@@ -125,11 +125,69 @@ def case_async_counting(rank, world, optimizer):
             b, e = tr.plan.shard_range[sh]
             assert torch.allclose(tr.params.flat[b:e], exp[b:e], atol=1e-4), "lost or duplicated update in shard %d" % sh
     else:
-        assert st["shard_version"] >= 1 and st["optimizer_steps"] >= 1, st
+        # one optimizer step per push (mnist_async/parameter_server.py:55-69), except pushes of ONE worker that
+        # landed twice between two applies of an owner (summed in its plane; counted)
+        assert st["optimizer_steps"] + st["folded_pushes"] == K * world, st
+        assert st["shard_version"] == st["optimizer_steps"], st
         acc = t.mem["accum"].tensor()
         assert float(acc.abs().max()) == 0.0, "accumulator not drained"
         assert not torch.equal(tr.params.flat, init)
     t.close()
+
+
+def case_async_parity(rank, world, fold):
+    """Serialized pushes against the sequential-PS oracle.  Parity mode: push, apply, repeat - every push is one
+    optimizer step, exactly SequentialPS.async_push (mnist_async/parameter_server.py:55-69).  Fold mode: all ranks
+    push, then one apply - one step on the summed gradient."""
+    from ddl_b200.models.oracle import SequentialPS
+    cfg = base_cfg(mode="async", shard="greedy", num_ps=world, num_workers=world, transport="fused",
+                   optimizer="adam", lr=1e-2, variant="mnist_async_sharding_greedy", async_fold=fold)
+    tr = SPMDTrainer(cfg, rank, world, rank, "colocated")
+    t = tr.transport
+    ps = SequentialPS(tr.params.flat.cpu(), "adam", lr=1e-2)
+    rounds = 3
+    gens = [torch.Generator().manual_seed(1000 + r) for r in range(world)]
+
+    def grad_of(r):
+        return torch.randn(tr.grads.flat.shape, generator=gens[r])
+
+    def sync():
+        torch.cuda.synchronize()
+        dist.barrier()
+
+    for _ in range(rounds):
+        gs = [grad_of(r) for r in range(world)]          # every rank draws all of them: same streams everywhere
+        if fold:
+            tr.grads.flat.copy_(gs[rank])
+            native_push(t)
+            sync()
+            t.apply_pending()
+            sync()
+            ps.async_push(sum(gs))
+        else:
+            for r in range(world):
+                if rank == r:
+                    tr.grads.flat.copy_(gs[r])
+                    native_push(t)
+                sync()
+                t.apply_pending()
+                sync()
+                ps.async_push(gs[r])
+    t.pull_all()
+    sync()
+    st = t.stats()
+    steps = rounds if fold else rounds * world
+    assert st["optimizer_steps"] == steps, st
+    assert st["folded_pushes"] == (rounds * (world - 1) if fold else 0), st
+    diff = (tr.params.flat.cpu() - ps.p).abs().max().item()
+    assert diff < 2e-6, "async %s: parameters differ from the sequential PS by %g" % ("fold" if fold else "parity", diff)
+    t.close()
+
+
+def native_push(t):
+    import ctypes as C
+    from ddl_b200.ops import native
+    native.check(t.L.ddl_async_push(C.byref(t.comm), C.byref(t.async_args), native.stream_ptr()), "ddl_async_push")
 
 
 def case_async_train(rank, world):
@@ -173,6 +231,9 @@ def main():
         case_async_counting(rank, world, "sgd")
     elif case == "async_adam":
         case_async_counting(rank, world, "adam")
+    elif case == "async_parity":
+        case_async_parity(rank, world, fold=False)
+        case_async_parity(rank, world, fold=True)
     elif case == "async_train":
         case_async_train(rank, world)
     else:

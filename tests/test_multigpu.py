@@ -10,7 +10,11 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def run_case(case, nproc=2, timeout=300):
+NPROC = int(os.environ.get("DDL_TEST_NPROC", "2"))     # 2, 4 or 8 (profiles/mgpu_tests_n*.log are runs of this file)
+
+
+def run_case(case, nproc=None, timeout=300):
+    nproc = nproc or NPROC
     port = 29600 + (abs(hash(case)) % 200)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py"), case]
@@ -18,6 +22,6 @@ def run_case(case, nproc=2, timeout=300):
     assert r.returncode == 0 and "MGPU_OK " + case in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
-@pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "sync_vs_nccl", "sync_nvls_off", "sync_nvls_on", "async_sgd", "async_adam", "async_train"])
+@pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "sync_vs_nccl", "sync_nvls_off", "sync_nvls_on", "async_sgd", "async_adam", "async_parity", "async_train"])
 def test_fused_transport(case):
     run_case(case)

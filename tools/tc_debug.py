@@ -1,5 +1,6 @@
 """GPU diagnostic for the tcgen05 kernels: prints error maps so a layout / descriptor bug can be
 read off one run.  usage: python tools/tc_debug.py"""
+import os; os.environ.setdefault("DDL_LAB", "1")   # needs the instrumented library (ops/build.py --lab)
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

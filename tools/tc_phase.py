@@ -1,4 +1,5 @@
 """Phase timeline (globaltimer, ns) of CTA (0,0,0) of one act-GEMM launch.  usage: python tools/tc_phase.py"""
+import os; os.environ.setdefault("DDL_LAB", "1")   # needs the instrumented library (ops/build.py --lab)
 import os, sys, ctypes as C
 os.environ["DDL_TC_TRACE"] = "1"; os.environ["DDL_TC_DEBUG"] = str(16 | int(os.environ.get("EXTRA_DEBUG", "0")))
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

@@ -1,3 +1,4 @@
+import os; os.environ.setdefault("DDL_LAB", "1")   # needs the instrumented library (ops/build.py --lab)
 import os, sys, ctypes as C
 os.environ["DDL_TC_TRACE"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

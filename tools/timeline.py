@@ -1,6 +1,6 @@
 """Device timeline of one graph-replayed training step (1 GPU): every kernel's stream, start offset and duration,
 from CUPTI activity records (torch.profiler).  Diagnosis only - timings under a profiler are never reported as
-results.  usage: python tools/timeline.py [--steps 3]"""
+results.  usage: python tools/timeline.py [--steps 3]   (or under torchrun for a multi-rank step; rank 0 prints)"""
 import argparse, os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -13,11 +13,12 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--out", default="")
     a = ap.parse_args()
-    cfg = Config(variant="mnist_sync_sharding_greedy", mode="sync", shard="greedy", num_ps=1, num_workers=1, transport="fused",
-                 backend="native", synthetic=True, synthetic_train=6000, synthetic_test=1000, seed=1234, eval_every=0,
-                 graphs=True, log_time=False).validate()
-    tr = SPMDTrainer(cfg, 0, 1, 0, "auto")
-    nb = tr.data.batches_per_epoch(cfg.batch_size, 1, False)
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))   # torchrun: one timeline per rank
+    cfg = Config(variant="mnist_sync_sharding_greedy", mode="sync", shard="greedy", num_ps=world, num_workers=world,
+                 transport="fused", backend="native", synthetic=True, synthetic_train=6000, synthetic_test=1000, seed=1234,
+                 eval_every=0, graphs=True, log_time=False).validate()
+    tr = SPMDTrainer(cfg, rank, world, rank, "colocated" if world > 1 else "auto")
+    nb = tr.data.batches_per_epoch(cfg.batch_size, world, False)
     for i in range(8):
         tr.train_step(i % nb)
     torch.cuda.synchronize()
@@ -39,6 +40,8 @@ def main():
         name = e.name.replace("(anonymous namespace)::", "").replace("<unnamed>::", "")
         rows.append({"name": name[:44], "start_us": round(e.time_range.start - t0, 1),
                      "dur_us": round(e.time_range.elapsed_us(), 1), "end_us": round(e.time_range.end - t0, 1)})
+    if rank != 0:
+        return
     for r in rows:
         print("%8.1f  +%6.1f  -> %8.1f  %s" % (r["start_us"], r["dur_us"], r["end_us"], r["name"]))
     if a.out:

@@ -1,5 +1,6 @@
 """clock64 stamps of CTA (0,0,0) of one tc_wgrad launch: per pixel-tile iteration the producer's issue window and the
 MMA warp's wait / issue windows, plus prologue / epilogue.  usage: python tools/wgrad_trace.py"""
+import os; os.environ.setdefault("DDL_LAB", "1")   # needs the instrumented library (ops/build.py --lab)
 import os, sys, ctypes as C
 os.environ["DDL_TC_TRACE"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
