@@ -90,8 +90,29 @@ def case_sync_vs_nccl(rank, world, layout_kind, shard, opt, nvls="auto"):
         results[transport] = tr.params.flat.clone()
         tr.transport.close()
     if rank in tr.layout.worker_ranks:
+        # compare the variables only: the arena also holds alignment padding (between variables, and at the end of a
+        # flat plan) that the test fills with random "gradients"; the bucketed fused transport never touches the
+        # padding outside its variables' ranges, the collective rung updates whole shards
+        mask = torch.zeros_like(results["fused"], dtype=torch.bool)
+        for v in range(tr.spec.num_vars):
+            mask[tr.plan.var_offset[v]:tr.plan.var_offset[v] + tr.spec.vars[v].numel] = True
+        results = {k: torch.where(mask, x, torch.zeros_like(x)) for k, x in results.items()}
         diff = (results["fused"] - results["nccl"]).abs().max().item()
-        assert diff < 2e-6, "fused vs nccl parameter difference %g (%s, %s)" % (diff, shard, opt)
+        # Two ranks: one possible summation order, the two paths agree to rounding of the optimizer arithmetic.  More
+        # ranks: NCCL's ring / tree order, the fixed ascending-rank order of the peer-load path and the in-switch order
+        # of multimem.ld_reduce all differ, and Adam's normalised step (lr * m / sqrt(v), magnitude ~lr whatever |g|) turns
+        # a 1e-7 relative difference of a nearly cancelling sum into a visible one (1.65e-5 measured at 4 ranks, lr 1e-2).
+        # 2e-4 is 2% of ONE step: a dropped or doubled rank moves parameters by ~1e-2.
+        tol = 2e-6 if world <= 2 else 2e-4
+        if diff >= tol:                       # say where: arena index, owning shard, variable, how many elements
+            d = (results["fused"] - results["nccl"]).abs()
+            i = int(d.argmax().item())
+            sh = [k for k, (b, e) in enumerate(tr.plan.shard_range) if b <= i < e]
+            var = [v for v in range(tr.spec.num_vars) if tr.plan.var_offset[v] <= i < tr.plan.var_offset[v] + tr.spec.vars[v].numel]
+            bad = (d >= tol).nonzero().flatten()
+            raise AssertionError("fused vs nccl parameter difference %g (%s, %s) at arena[%d] shard %s var %s; %d elements "
+                                 "off, first %d last %d; shard ranges %s" % (diff, shard, opt, i, sh, var, bad.numel(),
+                                                                            int(bad[0]), int(bad[-1]), tr.plan.shard_range))
     dist.barrier()
 
 
@@ -195,7 +216,8 @@ def case_async_train(rank, world):
                    variant="mnist_async_sharding_greedy", max_steps=6)
     tr = SPMDTrainer(cfg, rank, world, rank, "colocated")
     stats = tr.run()
-    assert stats["transport_stats"]["pushes_received"] == 6 * world, stats
+    # every worker pushes once per step to every owner (steps = min(max_steps, batches per epoch at this world size))
+    assert stats["steps"] >= 1 and stats["transport_stats"]["pushes_received"] == stats["steps"] * world, stats
     assert 0.0 <= stats["final_accuracy"] <= 1.0
     tr.transport.close()
 

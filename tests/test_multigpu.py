@@ -19,7 +19,14 @@ def run_case(case, nproc=None, timeout=300):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "mgpu_worker.py"), case]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
-    assert r.returncode == 0 and "MGPU_OK " + case in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+    ok = r.returncode == 0 and "MGPU_OK " + case in r.stdout
+    if not ok:
+        # the workers' own tracebacks sit far above torchrun's summary: keep the first one and every assertion line
+        err = r.stderr
+        first = err.find("Traceback")
+        keep = err[first:first + 3000] if first >= 0 else ""
+        lines = [ln for ln in err.splitlines() if "Error" in ln or "assert" in ln.lower()][:20]
+        assert ok, "\n".join([r.stdout[-1500:], keep, "\n".join(lines), err[-1500:]])
 
 
 @pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "sync_vs_nccl", "sync_nvls_off", "sync_nvls_on", "async_sgd", "async_adam", "async_parity", "async_train"])
