@@ -97,7 +97,108 @@ def parse():
     ap.add_argument("--no-overlap", action="store_true", help="disable the backward-overlapped (bucketed) push")
     ap.add_argument("--k4", action="store_true", help="enable the pull fused into the fc1/fc2 GEMMs (K4)")
     ap.add_argument("--no-k4", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--layout", default="colocated", choices=["colocated", "dedicated"],
+                    help="colocated: every GPU is a PS shard AND a worker; dedicated: --num-ps GPUs hold the shards, the "
+                         "other GPUs are workers (BASELINE config 2: 1 PS shard + 7 workers = --gpus 8 --layout dedicated --num-ps 1)")
+    ap.add_argument("--num-ps", type=int, default=0, help="number of PS shards (default: one per GPU; 1 for unsharded variants)")
+    ap.add_argument("--eval-every", type=int, default=0,
+                    help="also time a loop that evaluates the whole test set every E steps inside the timed region, as the "
+                         "reference's workers do (mnist_sync/worker.py:71-72: E = 10, 10,000 rows)")
+    ap.add_argument("--test-rows", type=int, default=10000)
+    ap.add_argument("--async-fold", action="store_true", help="async: one optimizer step on the sum of all pending pushes")
+    ap.add_argument("--no-exposed", action="store_true", help="skip the exposed push/pull measurement (a second, local-only run)")
     return ap.parse_args()
+
+
+def correctness_fields(tr, cfg, world, a, torch, dist):
+    """Every bench run is also a correctness run (distributed tier): sync - all workers hold bitwise-identical
+    parameters after the timed steps (64-bit position-weighted checksums of the whole arena, compared across ranks);
+    async - every push was received by every owner, and optimizer steps + folded pushes account for all of them."""
+    out = {}
+    lay = tr.layout
+    dev = tr.device
+    if hasattr(tr.transport, "ensure_local"):
+        tr.transport.ensure_local()
+    torch.cuda.synchronize()
+    if cfg.mode == "sync":
+        bits = tr.params.flat.view(torch.int32).to(torch.int64)
+        w = (torch.arange(bits.numel(), device=dev, dtype=torch.int64) % 65521) + 1
+        mine = torch.stack([bits.sum(), (bits * w).sum()])
+        allc = [torch.zeros_like(mine) for _ in range(world)]
+        if world > 1:
+            dist.all_gather(allc, mine)
+        else:
+            allc = [mine]
+        wr = lay.worker_ranks
+        out["params_bitwise_equal"] = bool(all(torch.equal(allc[wr[0]], allc[r]) for r in wr))
+        out["params_checksum"] = "%016x" % (int(allc[wr[0]][1].item()) & 0xFFFFFFFFFFFFFFFF)
+        out["ranks_compared"] = len(wr)
+    else:
+        st = tr.transport.stats() if hasattr(tr.transport, "stats") else {}
+        ok = 1
+        if lay.my_shards and "pushes_received" in st:
+            expect = tr.global_step * lay.num_workers
+            ok = int(st["pushes_received"] == expect)
+            if cfg.optimizer != "sgd" and "folded_pushes" in st:
+                ok &= int(st["optimizer_steps"] + st["folded_pushes"] == expect)
+        t = torch.tensor([ok], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        out["async_all_pushes_applied"] = bool(int(t.item()) == 1)
+        out["pushes_expected_per_owner"] = tr.global_step * lay.num_workers
+    return out
+
+
+def timed_with_eval(tr, a, nb, B, num_workers, world, is_worker, sync_all, torch, dist, dev):
+    """The reference's timed region (mnist_sync/worker.py:45-74) contains a full-test-set evaluation every 10 batches:
+    the same K steps again, with ``evaluate()`` (forward of all test rows + accuracy read on the host) every E steps."""
+    sync_all()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    acc, evals = None, 0
+    for i in range(a.steps):
+        tr.train_step((a.warmup + 2 * a.steps + i) % nb)
+        if i % a.eval_every == 0 and is_worker:
+            acc = tr.evaluate()
+            evals += 1
+    e1.record()
+    sync_all()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    rows = int(tr.x_test.shape[0]) if is_worker else 0
+    return {"value": a.steps * B * num_workers / (ms / 1e3), "unit": "samples/s", "ms_per_step": ms / a.steps,
+            "eval_every": a.eval_every, "test_rows": rows, "evaluations": evals, "last_accuracy": acc,
+            "timing": "CUDA events around the whole loop (evaluations included), max over ranks; L2 not flushed inside"}
+
+
+def exposed_push_pull(cfg, a, local, world, ms_step, sync_all, torch, dist, dev, flush):
+    """Exposed push / pull time per step = step time at N ranks minus the time of the same step with the transport
+    replaced by a local optimizer: every rank runs the identical engine + fused update kernels as a world of ONE (its
+    own gradients, no peer traffic, no barriers), same batch, same graph capture, same L2 flush."""
+    if world == 1:
+        return {"exposed_push_pull_ms": 0.0, "local_only_ms_per_step": ms_step}
+    from ddl_b200.parallel.trainer import SPMDTrainer
+    cfg1 = cfg.replace(num_ps=1, num_workers=1, fused_pull_gemm=False, nvls="off")
+    tr1 = SPMDTrainer(cfg1, 0, 1, local)
+    nb1 = tr1.data.batches_per_epoch(cfg.batch_size, 1, False)
+    for i in range(max(5, a.warmup)):
+        tr1.train_step(i % nb1)
+    sync_all()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    for i in range(a.steps):
+        if flush is not None:
+            flush.fill_(i & 0xFF)
+        evs[i][0].record()
+        tr1.train_step((a.warmup + i) % nb1)
+        evs[i][1].record()
+    sync_all()
+    t = torch.tensor([sum(s.elapsed_time(e) for s, e in evs) / a.steps], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_local = float(t.item())
+    tr1.transport.close()
+    return {"exposed_push_pull_ms": ms_step - ms_local, "local_only_ms_per_step": ms_local}
 
 
 def main() -> int:
@@ -140,20 +241,27 @@ def main() -> int:
 
     mode, shard = VARIANTS[a.variant]
     shard = a.shard or shard
-    if shard == "none" and world > 1:
-        num_ps = 1
+    dedicated = a.layout == "dedicated" and world > 1
+    if dedicated:
+        num_ps = a.num_ps or 1
+        num_workers = world - num_ps
+        if num_workers < 1:
+            raise SystemExit("--layout dedicated needs --gpus > --num-ps")
+        if num_ps == 1:
+            shard = "none"
     else:
-        num_ps = world
+        num_ps = a.num_ps or (1 if (shard == "none" and world > 1) else world)
+        num_workers = world
     transport = {"ours": "fused", "nccl": "nccl", "torch": "nccl" if world > 1 else "local"}[a.impl]
     backend = "torch" if a.impl == "torch" else "native"
-    cfg = Config(variant=a.variant, mode=mode, shard=shard, num_ps=num_ps, num_workers=world,
+    test_rows = a.test_rows if a.eval_every else 1000
+    cfg = Config(variant=a.variant, mode=mode, shard=shard, num_ps=num_ps, num_workers=num_workers,
                  batch_size=a.batch_size, optimizer=a.optimizer, transport=transport, backend=backend,
-                 synthetic=True, synthetic_train=max(6000, a.batch_size * 32), synthetic_test=1000, seed=1234,
+                 synthetic=True, synthetic_train=max(6000, a.batch_size * 32), synthetic_test=test_rows, seed=1234,
                  eval_every=0, width_mult=a.width_mult, graphs=not a.no_graphs, log_time=False,
-                 fused_pull_gemm=a.k4 and not a.no_k4, overlap_push=not a.no_overlap, nvls=a.nvls).validate()
-    kind = "colocated" if world > 1 else "auto"
-    if world > 1 and num_ps == 1:
-        kind = "colocated"
+                 fused_pull_gemm=a.k4 and not a.no_k4, overlap_push=not a.no_overlap, nvls=a.nvls,
+                 async_fold=a.async_fold).validate()
+    kind = ("dedicated" if dedicated else "colocated") if world > 1 else "auto"
     # nvidia-smi sampler (every 20 ms) is started before anything else: it needs up to a second to produce its
     # first row on an 8-GPU box, longer than a short timed region
     sampler = ClockSampler(local)
@@ -162,7 +270,8 @@ def main() -> int:
     tr = SPMDTrainer(cfg, rank, world, local, kind)
     dev = tr.device
     B = cfg.batch_size
-    nb = tr.data.batches_per_epoch(B, world, False)
+    is_worker = tr.layout.is_worker
+    nb = tr.data.batches_per_epoch(B, num_workers, False) if tr.data is not None else 1 << 30
 
     def sync_all():
         torch.cuda.synchronize()
@@ -208,6 +317,8 @@ def main() -> int:
     for i in range(a.steps):
         loss = tr.train_step((a.warmup + a.steps + i) % nb)         # H2D from pinned memory inside
         slot = i & 1
+        if loss is None:                                              # a PS-only rank (dedicated layout) has no loss
+            continue
         if done[slot] is not None:                                    # read the loss of step i-2 (pipelined D2H)
             done[slot].synchronize()
             losses.append(float(host_loss[slot]))
@@ -229,12 +340,34 @@ def main() -> int:
     clocks = sampler.stop(t_load_begin, time.time())
     if hasattr(tr.transport, "finish"):
         tr.transport.finish()                 # async: drain accumulators, final pull
-    acc = tr.evaluate()
+    acc = tr.evaluate() if is_worker else float("-inf")
     stats = tr.transport.stats() if hasattr(tr.transport, "stats") else {}
+    extra = {}
+    try:
+        extra.update(correctness_fields(tr, cfg, world, a, torch, dist))
+    except Exception as e:                    # noqa: BLE001 - the headline line must survive a failing extra
+        extra["correctness_error"] = repr(e)[:300]
+    if a.eval_every > 0:
+        try:
+            extra["with_eval"] = timed_with_eval(tr, a, nb, B, num_workers, world, is_worker, sync_all, torch, dist, dev)
+        except Exception as e:                # noqa: BLE001
+            extra["with_eval"] = {"error": repr(e)[:300]}
+    if a.impl == "ours" and not a.no_exposed:
+        try:
+            extra.update(exposed_push_pull(cfg, a, local, world, dev_ms / a.steps, sync_all, torch, dist, dev, flush))
+        except Exception as e:                # noqa: BLE001
+            extra["exposed_push_pull_error"] = repr(e)[:300]
+    # rank 0 prints; in the dedicated layout it is a PS-only rank, so the workers' numbers are reduced to it
+    red = torch.tensor([losses[0] if losses else float("-inf"), losses[-1] if losses else float("-inf"), acc],
+                       device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+    first_loss, final_loss, acc = (None if v == float("-inf") else v for v in red.tolist())
+    spec_params, tname, k4on = tr.spec.num_params, tr.transport.name, bool(getattr(tr.transport, "k4_src", None))
     tr.close()
 
     if rank == 0:
-        total = a.steps * B * world
+        total = a.steps * B * num_workers
         h2d = B * 784 * 4 + B * 4
         out = {
             "metric": "samples/sec", "value": total / (dev_ms / 1e3), "unit": "samples/s", "n_gpus": world,
@@ -244,20 +377,21 @@ def main() -> int:
             "data": "synthetic MNIST-shaped [N,784] fp32, 10 classes; random-init (glorot) weights",
             "impl": a.impl,
             "config": {"model": "mnist_cnn_14var" + ("" if a.width_mult == 1 else "_x%d" % a.width_mult),
-                       "params": tr.spec.num_params, "variant": a.variant, "mode": mode, "shard": shard,
-                       "global_batch": B * world, "batch_per_worker": B, "seq_len": None,
-                       "parallelism": "ps%d+w%d colocated, %s transport" % (num_ps, world, tr.transport.name),
+                       "params": spec_params, "variant": a.variant, "mode": mode, "shard": shard,
+                       "global_batch": B * num_workers, "batch_per_worker": B, "seq_len": None,
+                       "parallelism": "ps%d+w%d %s, %s transport" % (num_ps, num_workers, "dedicated" if dedicated else "colocated", tname),
                        "optimizer": a.optimizer, "keep_prob": cfg.keep_prob,
                        "l2": "256 MiB written between timed steps" if flush is not None else "not flushed",
                        "cuda_graph": graph_mode, "backend": backend,
-                       "k4_fused_pull_gemm": bool(getattr(tr.transport, "k4_src", None))},
+                       "k4_fused_pull_gemm": k4on},
             "clocks": clocks,
             "e2e": {"value": total / e2e_s, "unit": "samples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": e2e_s * 1e3 / a.steps},
             "gpu_launches": int(launches),
-            "final_loss": losses[-1] if losses else None, "first_loss": losses[0] if losses else None,
+            "final_loss": final_loss, "first_loss": first_loss,
             "test_accuracy_after_bench": acc, "transport_stats": stats,
         }
+        out.update(extra)
         emit(out)
     return 0
 
