@@ -273,7 +273,25 @@ def main() -> int:
     is_worker = tr.layout.is_worker
     nb = tr.data.batches_per_epoch(B, num_workers, False) if tr.data is not None else 1 << 30
 
+    # Async + dedicated PS GPUs: the PS rank serves pushes from a resident kernel that ends only on request, and no NCCL
+    # collective may be issued on that GPU while it runs.  Phase boundaries there are: (1) a host barrier through the
+    # TCP store - every worker has finished the phase and synchronised its device, (2) the PS rank stops the resident
+    # kernel (it drains what is pending first), (3) the usual device sync + NCCL barrier.  The PS rank's next
+    # train_step starts the kernel again.
+    store_sync = world > 1 and mode == "async" and dedicated and a.impl == "ours"
+    phase = [0]
+
     def sync_all():
+        if store_sync:
+            (torch.cuda.synchronize if is_worker else torch.cuda.current_stream().synchronize)()
+            store = dist.distributed_c10d._get_default_store()
+            phase[0] += 1
+            key = "bench_phase_%d" % phase[0]
+            store.add(key, 1)
+            while store.add(key, 0) < world:
+                time.sleep(0.0005)
+            if hasattr(tr.transport, "stop_resident"):
+                tr.transport.stop_resident()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()

@@ -433,6 +433,115 @@ async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const DdlAsyncState* as
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Resident owner (dedicated async PS GPU): ONE launch that stays on the device and serves pushes as they land - the
+// reference's ``while`` loop of mnist_async/parameter_server.py:52-69, without a host in it.  Round r:
+//   block 0 / thread 0 polls the per-worker push counters (and the host's stop word); when something is pending it
+//   takes the snapshot (same rules as async_snapshot_kernel), publishes round r with a release store;
+//   every block waits for round r, applies its slice (one optimizer step per pending push, planes consumed with
+//   atomicExch), bumps the done counter; block 0 collects the bumps, publishes the shard version (+ nsteps) and goes
+//   back to polling.
+// All blocks must be co-resident (the host sizes the grid from the occupancy API).  Idle polling is bounded:
+// DDL_WAIT_TIMEOUT_NS x 16 without a push or a stop traps.
+// ------------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(kCommThreads)
+async_owner_resident_kernel(const DdlComm c, const DdlSyncArgs a, DdlAsyncState* as, DdlResident* rs, const int nworkers,
+                            const int64_t slot_stride, const int fold, const float b1, const float b2) {
+  __shared__ uint32_t s_stop;
+  float* myp = c.params[c.rank];
+  float* acc = c.accum[c.rank];
+  const int64_t n4 = (a.end - a.begin) / 4;
+  for (uint32_t round = 1;; ++round) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      uint32_t spins = 0, mask = 0, nsteps = 0, stop = 0;
+      uint64_t t0 = 0;
+      for (;;) {
+        uint32_t t = a.st->t;
+        mask = 0; nsteps = 0;
+        for (int w = 0; w < nworkers; ++w) {
+          const uint32_t cnt = ld_acquire_sys(c.pads[c.rank] + DDL_PAD_PUSHES_W + w);
+          const uint32_t n = cnt - as->applied[w];
+          if (n) {
+            as->applied[w] = cnt;
+            mask |= 1u << w;
+            as->folded += n - 1;
+            if (!fold || nsteps == 0) {
+              ++t;
+              as->lr_t[nsteps] = (float)((double)a.lr * sqrt(1.0 - pow((double)b2, (double)t)) / (1.0 - pow((double)b1, (double)t)));
+              ++nsteps;
+            } else {
+              as->folded += 1;
+            }
+          }
+        }
+        if (mask) { a.st->t = t; a.st->lr_t = as->lr_t[nsteps - 1]; break; }
+        if ((++spins & 0x3f) == 0) {
+          uint32_t hv;                                   // the host's stop word lives in pinned host memory
+          asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(hv) : "l"(rs->host_stop) : "memory");
+          if (hv) { stop = 1; break; }
+          const uint64_t now = ddl_globaltimer();
+          if (t0 == 0) t0 = now;
+          else if (now - t0 > 16 * DDL_WAIT_TIMEOUT_NS) { printf("[ddl] resident owner %d: idle too long\n", c.rank); __trap(); }
+        }
+      }
+      as->mask = mask;
+      as->nsteps = nsteps;
+      rs->stop = stop;
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&rs->round), "r"(round) : "memory");
+    }
+    if (threadIdx.x == 0) {
+      uint32_t seen;
+      do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(&rs->round) : "memory"); } while (seen != round);
+      s_stop = rs->stop;
+    }
+    __syncthreads();
+    if (s_stop) return;
+    const uint32_t mask = as->mask;
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < n4; q += (int64_t)gridDim.x * blockDim.x) {
+      const int64_t i = a.begin + q * 4;
+      float4 pv = *reinterpret_cast<float4*>(myp + i);
+      float4 mv = make_float4(0.f, 0.f, 0.f, 0.f), vv = mv;
+      if (KIND >= 1) mv = *reinterpret_cast<float4*>(a.m + i);
+      if (KIND == 2) vv = *reinterpret_cast<float4*>(a.v + i);
+      float4 gs = make_float4(0.f, 0.f, 0.f, 0.f);
+      int k = 0;
+#pragma unroll 1
+      for (int w = 0; w < nworkers; ++w) {
+        if (!((mask >> w) & 1u)) continue;
+        float* pl = acc + (int64_t)w * slot_stride + i;
+        float4 g;
+        g.x = atomicExch(pl, 0.f); g.y = atomicExch(pl + 1, 0.f); g.z = atomicExch(pl + 2, 0.f); g.w = atomicExch(pl + 3, 0.f);
+        if (fold) { gs.x += g.x; gs.y += g.y; gs.z += g.z; gs.w += g.w; continue; }
+        g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
+        pv = opt_math<KIND>(pv, g, mv, vv, KIND == 2 ? as->lr_t[k] : a.lr, a.a, a.b, a.eps);
+        ++k;
+      }
+      if (fold) {
+        gs.x *= a.gscale; gs.y *= a.gscale; gs.z *= a.gscale; gs.w *= a.gscale;
+        pv = opt_math<KIND>(pv, gs, mv, vv, KIND == 2 ? as->lr_t[0] : a.lr, a.a, a.b, a.eps);
+      }
+      if (KIND >= 1) *reinterpret_cast<float4*>(a.m + i) = mv;
+      if (KIND == 2) *reinterpret_cast<float4*>(a.v + i) = vv;
+      *reinterpret_cast<float4*>(myp + i) = pv;
+    }
+    // grid barrier: every block's stores are fenced before its bump; block 0 publishes the new version after the last one
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      atomicAdd(&rs->done, 1u);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      uint32_t seen;
+      do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(&rs->done) : "memory"); } while (seen != gridDim.x * round);
+      __threadfence_system();
+      atom_add_release_sys(c.pads[c.rank] + DDL_PAD_VERSION, as->nsteps);
+      rs->rounds_served = round;
+    }
+  }
+}
+
 // K3: worker copies every owner's range into its own parameter arena (peer loads, no barrier).
 __global__ void __launch_bounds__(kCommThreads)
 pull_allgather_kernel(const DdlComm c, const DdlAsyncArgs a) {
@@ -652,6 +761,29 @@ int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, DdlAsyncSt
   else if (kind == 1) DDL_LAUNCH(async_apply_kernel<1>, grid, kCommThreads, 0, s, *c, *a, (const DdlAsyncState*)state, nworkers, slot_stride, fold);
   else DDL_LAUNCH(async_apply_kernel<2>, grid, kCommThreads, 0, s, *c, *a, (const DdlAsyncState*)state, nworkers, slot_stride, fold);
   DDL_LAUNCH_CHECK();
+  return 0;
+}
+
+/* Starts the resident owner kernel on stream s (a stream of its own: it runs until *host_stop != 0).  The grid is sized
+ * so that every block is resident at once (occupancy API), at most two blocks per SM. */
+int ddl_async_owner_start(const DdlComm* c, const DdlSyncArgs* a, int kind, DdlAsyncState* state, DdlResident* resident,
+                          int nworkers, int64_t slot_stride, int fold, float b1, float b2, cudaStream_t s) {
+  DDL_REQUIRE(nworkers >= 1 && nworkers <= DDL_MAX_PEERS, "ddl_async_owner_start: %d workers out of range", nworkers);
+  int dev = 0, sms = 0, per_sm = 0;
+  DDL_CHECK_CUDA(cudaGetDevice(&dev));
+  DDL_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const void* fn = kind == 0 ? (const void*)async_owner_resident_kernel<0>
+                 : kind == 1 ? (const void*)async_owner_resident_kernel<1> : (const void*)async_owner_resident_kernel<2>;
+  DDL_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kCommThreads, 0));
+  DDL_REQUIRE(per_sm >= 1, "ddl_async_owner_start: the resident kernel does not fit an SM");
+  int grid = sms * (per_sm > 2 ? 2 : per_sm);
+  const int want = comm_grid(a->end - a->begin);
+  if (grid > want) grid = want;
+  if (kind == 0) async_owner_resident_kernel<0><<<grid, kCommThreads, 0, s>>>(*c, *a, state, resident, nworkers, slot_stride, fold, b1, b2);
+  else if (kind == 1) async_owner_resident_kernel<1><<<grid, kCommThreads, 0, s>>>(*c, *a, state, resident, nworkers, slot_stride, fold, b1, b2);
+  else async_owner_resident_kernel<2><<<grid, kCommThreads, 0, s>>>(*c, *a, state, resident, nworkers, slot_stride, fold, b1, b2);
+  DDL_LAUNCH_CHECK();
+  ddl::note_launch();
   return 0;
 }
 

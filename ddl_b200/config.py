@@ -81,6 +81,7 @@ class Config:
     nvls: str = "auto"              # auto | on | off: NVSwitch multicast (multimem.ld_reduce / multimem.st) for the sync push / pull
     async_fold: bool = False        # async + fused: one optimizer step on the SUM of all pending pushes (round-1 behaviour)
                                     # instead of one step per push (the reference's semantics, mnist_async/parameter_server.py:55-69)
+    resident_owner: bool = True     # async + fused, dedicated PS GPU: serve pushes from ONE resident kernel instead of host-launched applies
     overlap_push: bool = True       # sync + fused: push/update/pull conv3..fc3 (98% of the bytes) while conv2/conv1 backward runs
     timeout_s: float = 120.0        # collective / rendezvous timeout (failure detection)
     log_time: bool = True           # print the reference's "Time:" line
@@ -165,6 +166,8 @@ def build_parser(role: str = "worker") -> argparse.ArgumentParser:
                    default=_env_default("fused_pull_gemm", False))
     p.add_argument("--nvls", choices=("auto", "on", "off"), default=_env_default("nvls", "auto"))
     p.add_argument("--no-overlap-push", dest="overlap_push", action="store_false", default=True)
+    p.add_argument("--no-resident-owner", dest="resident_owner", action="store_false", default=True,
+                   help="async dedicated PS: host-launched apply kernels instead of the resident owner kernel")
     p.add_argument("--async-fold", dest="async_fold", action="store_true", default=_env_default("async_fold", False),
                    help="async + fused transport: fold all pushes pending at an apply into ONE optimizer step")
     p.add_argument("--timeout-s", type=float, default=_env_default("timeout_s", d.timeout_s))

@@ -175,6 +175,8 @@ class SPMDTrainer:
     # -- CUDA-graph fast path ------------------------------------------------------------
     @property
     def _graphable(self) -> bool:
+        if self.cfg.mode == "async" and not self.layout.is_worker:
+            return False          # an async PS-only rank starts a resident kernel / launches applies: nothing to replay
         return (self.device.type == "cuda" and self.transport.name == "fused"
                 and (self.model is None or self.model.backend == "native") and not self.cfg.profile)
 

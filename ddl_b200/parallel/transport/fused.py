@@ -396,9 +396,47 @@ class FusedTransport(SpmdTransport):
                 self.pull_all()
         self.step_count += 1
 
+    # -- resident owner (dedicated async PS GPU) ---------------------------------------------------
+    def _resident_eligible(self) -> bool:
+        lay, c = self.layout, self.cfg
+        return (c.mode == "async" and c.resident_owner and lay.kind == "dedicated" and not lay.is_worker
+                and len(lay.my_shards) == 1 and not self.async_args.direct_sgd and lay.world > 1)
+
+    def start_resident(self) -> None:
+        """Launches the resident owner kernel (csrc/comm.cu) on a stream of its own; it serves pushes until
+        ``stop_resident`` writes the pinned stop word."""
+        if getattr(self, "_resident", None) is not None:
+            return
+        c = self.cfg
+        dev = self.params.device
+        self._res_stop = torch.zeros(1, dtype=torch.int32).pin_memory()
+        res = torch.zeros(6, dtype=torch.int32, device=dev)         # DdlResident: 4 words + the host pointer
+        ptr = self._res_stop.data_ptr()
+        res[4] = int(C.c_int32(ptr & 0xFFFFFFFF).value)
+        res[5] = int(C.c_int32((ptr >> 32) & 0xFFFFFFFF).value)
+        self._res_dev = res
+        self._res_stream = torch.cuda.Stream(device=dev)
+        torch.cuda.current_stream().synchronize()                   # state tensors are initialised before the kernel polls
+        native.check(self.L.ddl_async_owner_start(C.byref(self.comm), C.byref(self.sync_args[0]), self.kind,
+                                                  self.async_state.data_ptr(), res.data_ptr(), self.layout.num_workers,
+                                                  self.plan.total, 1 if c.async_fold else 0, c.beta1, c.beta2,
+                                                  self._res_stream.cuda_stream), "ddl_async_owner_start")
+        self._resident = True
+
+    def stop_resident(self) -> None:
+        if getattr(self, "_resident", None):
+            self._res_stop[0] = 1
+            self._res_stream.synchronize()
+            self._resident = None
+
     def apply_pending(self) -> None:
         """Owner side of async mode: consume whatever has been pushed since the last call."""
         if self.async_args.direct_sgd or not self.layout.my_shards:
+            return
+        if getattr(self, "_resident", None):
+            return                               # the resident kernel is serving; two consumers must not race
+        if self._resident_eligible() and not getattr(self, "_resident_done", False):
+            self.start_resident()
             return
         c = self.cfg
         for a in self.sync_args:
@@ -413,6 +451,12 @@ class FusedTransport(SpmdTransport):
         store = dist.distributed_c10d._get_default_store()
         keys = ["ddl_done_%d" % wr for wr in self.layout.worker_ranks]
         rounds = 0
+        if self._resident_eligible():
+            import time
+            self.start_resident()
+            while not store.check(keys):         # the device serves; the host only waits for the workers to finish
+                time.sleep(0.002)
+            return 0
         while True:
             for _ in range(poll_every):
                 self.apply_pending()
@@ -428,9 +472,20 @@ class FusedTransport(SpmdTransport):
             if self.cfg.mode == "async":
                 self.apply_pending()
             return
+        store = dist.distributed_c10d._get_default_store()
         if self.layout.is_worker:
             torch.cuda.synchronize()
-            dist.distributed_c10d._get_default_store().set("ddl_done_%d" % self.layout.rank, "1")
+            store.set("ddl_done_%d" % self.layout.rank, "1")
+        if getattr(self, "_resident", None):
+            # No collective while the resident kernel runs (a NCCL barrier synchronises the device and would never
+            # return): wait for the workers' completion keys through the store, then let the kernel serve what is
+            # pending and stop it.  From here on the launch-based apply drains anything that is left.
+            import time
+            keys = ["ddl_done_%d" % wr for wr in self.layout.worker_ranks]
+            while not store.check(keys):
+                time.sleep(0.001)
+        self._resident_done = True
+        self.stop_resident()
         torch.cuda.synchronize()
         dist.barrier()                       # all pushes have landed
         self.apply_pending()
@@ -439,6 +494,13 @@ class FusedTransport(SpmdTransport):
         if self.layout.is_worker:
             self.pull_all()
         torch.cuda.synchronize()
+
+    def _sync(self) -> None:
+        """Device-wide synchronize, except while the resident owner kernel runs (it ends only on request)."""
+        if getattr(self, "_resident", None):
+            torch.cuda.current_stream().synchronize()
+        else:
+            torch.cuda.synchronize()
 
     # ------------------------------------------------------------------------------
     def loss(self, batch: int) -> torch.Tensor:
@@ -457,6 +519,8 @@ class FusedTransport(SpmdTransport):
             # pushes that shared an optimizer step with another push: a worker that pushed twice between two applies
             # (its plane holds the sum), or every extra push under --async-fold.  optimizer_steps + folded == pushes.
             out["folded_pushes"] = int(self.async_state[native.MAX_PEERS + 2].item())
+            if getattr(self, "_res_dev", None) is not None:
+                out["resident_rounds"] = int(self._res_dev[3].item())     # rounds served by the resident owner kernel
         return out
 
     def opt_state(self):
@@ -480,6 +544,7 @@ class FusedTransport(SpmdTransport):
         self.st[0] = int(t)
 
     def close(self) -> None:
+        self.stop_resident()
         torch.cuda.synchronize()
         if self.layout.world > 1 and dist.is_initialized():
             dist.barrier()

@@ -255,6 +255,15 @@ int ddl_async_push(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s);
  * applies Adam once per received gradient.  fold = 1: one step on the sum of all pending planes (round-1 behaviour). */
 int ddl_async_apply(const DdlComm* c, const DdlSyncArgs* a, int kind, DdlAsyncState* state, int nworkers,
                     int64_t slot_stride, int fold, float b1, float b2, cudaStream_t s);
+/* Resident owner of a dedicated async PS GPU (mnist_async/parameter_server.py:52-69 as ONE kernel that stays on the
+ * device): polls the per-worker push counters, applies one optimizer step per push as they land (fold = 1: one per
+ * round), publishes the shard version, until the host writes a non-zero word to *host_stop (pinned host memory). */
+typedef struct DdlResident {
+  uint32_t round, stop, done, rounds_served;   /* device words, zero-initialised */
+  const uint32_t* host_stop;                   /* pinned host word the kernel polls */
+} DdlResident;
+int ddl_async_owner_start(const DdlComm* c, const DdlSyncArgs* a, int kind, DdlAsyncState* state, DdlResident* resident,
+                          int nworkers, int64_t slot_stride, int fold, float b1, float b2, cudaStream_t s);
 /* K3 stand-alone (initial pull, async pull, pre-eval refresh). */
 int ddl_pull_allgather(const DdlComm* c, const DdlAsyncArgs* a, cudaStream_t s);
 int ddl_device_barrier(const DdlComm* c, uint32_t* epoch_counter, cudaStream_t s);

@@ -222,6 +222,31 @@ def case_async_train(rank, world):
     tr.transport.close()
 
 
+def case_async_dedicated(rank, world, resident):
+    """1 PS GPU + (world - 1) worker GPUs (BASELINE config 2, mnist_async/run.sh): the PS rank never touches data; with
+    ``resident`` its pushes are served by ONE kernel that stays on the device (no host loop), else by host-launched
+    applies.  Every push is received, and optimizer steps + folded pushes account for all of them."""
+    W = world - 1
+    cfg = base_cfg(mode="async", shard="none", num_ps=1, num_workers=W, transport="fused", variant="mnist_async",
+                   max_steps=6, resident_owner=resident)
+    tr = SPMDTrainer(cfg, rank, world, rank, "dedicated")
+    stats = tr.run()
+    ts = stats["transport_stats"]
+    if rank == 0:
+        assert not tr.layout.is_worker
+        assert ts["pushes_received"] == stats["steps"] * W, stats
+        assert ts["optimizer_steps"] + ts["folded_pushes"] == ts["pushes_received"], stats
+        if resident:
+            assert ts.get("resident_rounds", 0) >= 1, stats
+            if W == 1:
+                assert ts["folded_pushes"] <= stats["steps"] - 1, stats
+    allp = gather_flat(tr.params.flat.clone())
+    for r in range(2, world):
+        assert torch.equal(allp[1], allp[r]), "workers disagree after finish()"
+    assert torch.equal(allp[0], allp[1]), "worker parameters differ from the owner's after the final pull"
+    tr.transport.close()
+
+
 def main():
     case = sys.argv[1]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -256,6 +281,9 @@ def main():
     elif case == "async_parity":
         case_async_parity(rank, world, fold=False)
         case_async_parity(rank, world, fold=True)
+    elif case == "async_dedicated":
+        case_async_dedicated(rank, world, resident=True)
+        case_async_dedicated(rank, world, resident=False)
     elif case == "async_train":
         case_async_train(rank, world)
     else:
