@@ -225,6 +225,27 @@ DDL_DEVICE void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint3
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Predicated forms for WARP-UNIFORM issue loops: every lane runs the loop and computes the (uniform) descriptors, only the
+// instruction itself is predicated on the elected lane.  Inside an `if (elect_one()) { loop }` body the operands live in
+// per-thread registers and every tcgen05.mma pays a chain of R2UR moves (~100 cycles per MMA measured in the
+// patch-resident conv kernel, tools/patch_phase.py); with the loop outside the predicate ptxas keeps them in uniform
+// registers.
+DDL_DEVICE void umma_tf32_pred(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate, uint32_t issue) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "setp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(issue)
+      : "memory");
+}
+DDL_DEVICE void umma_commit_pred(uint64_t* bar, uint32_t issue) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "setp.ne.b32 q, %1, 0;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+      ::"r"(smem_u32(bar)), "r"(issue) : "memory");
+}
 // arrive on an mbarrier once every previously issued tcgen05.mma of this thread has completed
 DDL_DEVICE void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");

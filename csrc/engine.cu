@@ -22,11 +22,13 @@ inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 struct FwdPlans {                  // forward plans for one batch size
   int B = 0;
   DdlTcPlan* conv[3] = {nullptr, nullptr, nullptr};    // conv2..conv4
+  DdlPatchPlan* pconv[3] = {nullptr, nullptr, nullptr}; // ... or the patch-resident plan of the layer (tc_patch.cu)
   DdlTcPlan* fc[2] = {nullptr, nullptr};                // fc1, fc2
   int conv_split[3] = {1, 1, 1};
   bool fused_pool[3] = {false, false, false};           // conv plan's epilogue is bias + ReLU + pool
   void destroy() {
     for (auto& p : conv) { ddl_tc_plan_destroy(p); p = nullptr; }
+    for (auto& p : pconv) { ddl_patch_plan_destroy(p); p = nullptr; }
     for (auto& p : fc) { ddl_tc_plan_destroy(p); p = nullptr; }
   }
 };
@@ -59,6 +61,7 @@ struct DdlEngine {
   // backward plans (train batch only)
   DdlTcPlan* wg_conv[3] = {};
   DdlTcPlan* dg_conv[3] = {};
+  DdlPatchPlan* pdg_conv0 = nullptr;           // conv2's dgrad as a patch-resident plan (replaces dg_conv[0] when set)
   int dg_split[3] = {1, 1, 1};
   bool dg_unpool[3] = {false, false, false};   // dgrad plan's epilogue is the pool + ReLU backward of the layer below
   bool w1_pooled = false;                      // dg_conv[0] keeps conv1's gradient in the pooled layout (see build_bwd)
@@ -169,6 +172,16 @@ int build_fwd(DdlEngine* e, int B, bool train, FwdPlans* out) {
                                        nullptr, nullptr, 1.f, nullptr, 0, 1.f, nullptr, nullptr);
     if (!probe) return -1;
     int nt, ks;
+    if (fuse_pool_enabled() && ddl_patch_conv_preferred(S, S, cin, cout)) {
+      // large planes (conv2): one CTA per image, the padded activation patch resident in shared memory, every filter tap
+      // a shifted descriptor - the activation crosses L2 once instead of 25 times (csrc/tc_patch.cu)
+      ddl_tc_plan_destroy(probe);
+      out->pconv[l - 1] = ddl_patch_plan_create(0, e->pooled[l - 1], e->P(v), e->P(v + 1), e->pooled[l], train ? e->idx[l] : nullptr,
+                                                nullptr, B, S, S, cin, cout);
+      if (!out->pconv[l - 1]) return -1;
+      out->fused_pool[l - 1] = true;
+      continue;
+    }
     if (fuse_pool_enabled()) {
       // conv + bias + ReLU + pool in one kernel: no raw buffer, no zeroing, no pool launch
       ddl_tc_plan_destroy(probe);
@@ -252,6 +265,15 @@ int build_bwd(DdlEngine* e) {
         e->dg_conv[0] = ddl_tc_plan_dgrad_poolgrad(e->dfull[1], e->P(v), e->idx[0], e->dpool[0], e->G(1), B, S, S, cout, cin,
                                                    5, nt, ks);
         e->w1_pooled = e->dg_conv[0] != nullptr;
+        // The patch-resident dgrad is faster alone (29 vs 35 us) but slower inside the step (0.226 vs 0.217 ms): it runs
+        // beside conv2's wgrad, whose CTAs take whole SMs; one patch CTA per image also needs a whole SM each
+        // (208 KB), so 12 of the 100 wait for a second wave, while the tap-by-tap plan's 100 KB CTAs pack two per SM
+        // into what is free.  Kept for DDL_PATCH_DGRAD=1 experiments.
+        static const bool patch_dgrad = getenv("DDL_PATCH_DGRAD") != nullptr;
+        if (patch_dgrad && e->w1_pooled && ddl_patch_conv_preferred(S, S, cout, cin)) {
+          e->pdg_conv0 = ddl_patch_plan_create(1, e->dfull[1], e->P(v), nullptr, e->dpool[0], e->idx[0], e->G(1), B, S, S, cout, cin);
+          if (!e->pdg_conv0) return -1;
+        }
       } else {
         e->dg_conv[l - 1] = ddl_tc_plan_dgrad_unpool(e->dfull[l], e->P(v), e->idx[l - 1], e->dfull[l - 1],
                                                      l - 1 >= 1 ? e->G(v - 1) : nullptr, B, S, S, US, US, cout, cin, 5, nt, ks);
@@ -290,7 +312,7 @@ int forward(DdlEngine* e, FwdPlans* fp, const float* x, int B, bool train, cudaS
     for (int l = 1; l < e->nconv; ++l, v += 2) {
       const int S = e->S[l], cout = e->C[l + 1];
       if (fp->fused_pool[l - 1]) {
-        if (ddl_tc_plan_run(fp->conv[l - 1], s)) return -1;
+        if (fp->pconv[l - 1] ? ddl_patch_plan_run(fp->pconv[l - 1], s) : ddl_tc_plan_run(fp->conv[l - 1], s)) return -1;
         continue;
       }
       if (fp->conv_split[l - 1] > 1)
@@ -376,6 +398,7 @@ void ddl_engine_destroy(DdlEngine* e) {
   for (auto& kv : e->eval_fwd) kv.second.destroy();
   for (auto& p : e->wg_conv) ddl_tc_plan_destroy(p);
   for (auto& p : e->dg_conv) ddl_tc_plan_destroy(p);
+  ddl_patch_plan_destroy(e->pdg_conv0);
   for (auto& p : e->wg_fc) ddl_tc_plan_destroy(p);
   for (auto& p : e->dg_fc) ddl_tc_plan_destroy(p);
   for (void* p : e->allocs) cudaFree(p);
@@ -485,7 +508,7 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
       cudaStream_t wl = wstream(l);
       if (fork(wl)) return -1;
       if (ddl_tc_plan_run(e->wg_conv[l - 1], wl)) return -1;
-      if (ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
+      if ((l == 1 && e->pdg_conv0) ? ddl_patch_plan_run(e->pdg_conv0, s) : ddl_tc_plan_run(e->dg_conv[l - 1], s)) return -1;
       if (l == 3 && e->ov_n > 0 && launch_overlap_conv(1, wl, e->ev_fork2)) return -1;
       if (l == 2 && e->ov_n > 0 && launch_overlap_conv(2, wl, e->ev_main2)) return -1;
     }

@@ -102,6 +102,39 @@ def conv5x5_dgrad_poolgrad(dy: torch.Tensor, w: torch.Tensor, idx: torch.Tensor,
     return out, db
 
 
+def _run_patch_plan(plan):
+    if not plan:
+        raise native.NativeError("patch plan creation failed: " + native.last_error())
+    try:
+        native.check(native.lib().ddl_patch_plan_run(plan, native.stream_ptr()), "ddl_patch_plan_run")
+    finally:
+        native.lib().ddl_patch_plan_destroy(plan)
+
+
+def conv5x5_relu_pool_patch(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, want_idx: bool = True):
+    """conv + bias + ReLU + 2x2 SAME max-pool with the patch-resident kernel (csrc/tc_patch.cu); returns (pooled, idx)."""
+    N, H, W, Cin = x.shape
+    Cout = w.shape[3]
+    y = torch.empty(N, (H + 1) // 2, (W + 1) // 2, Cout, device=x.device, dtype=torch.float32)
+    idx = torch.empty(y.shape, device=x.device, dtype=torch.uint8) if want_idx else None
+    plan = native.lib().ddl_patch_plan_create(0, native.ptr(x), native.ptr(w), native.ptr(bias), native.ptr(y), native.ptr(idx),
+                                              None, N, H, W, Cin, Cout)
+    _run_patch_plan(plan)
+    return y, idx
+
+
+def conv5x5_dgrad_poolgrad_patch(dy: torch.Tensor, w: torch.Tensor, idx: torch.Tensor, want_db: bool = True):
+    """conv dgrad + ReLU mask of the layer below, gradient kept pooled, with the patch-resident kernel."""
+    N, H, W, Cout = dy.shape
+    Cin = w.shape[2]
+    out = torch.empty(N, H, W, Cin, device=dy.device, dtype=torch.float32)
+    db = torch.zeros(Cin, device=dy.device, dtype=torch.float32) if want_db else None
+    plan = native.lib().ddl_patch_plan_create(1, native.ptr(dy), native.ptr(w), None, native.ptr(out), native.ptr(idx),
+                                              native.ptr(db), N, H, W, Cout, Cin)
+    _run_patch_plan(plan)
+    return out, db
+
+
 def conv5x5_wgrad(dy: torch.Tensor, x: torch.Tensor, ksize: int = 5, ntile: int = 0, psplit: int = 1,
                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """conv2d backprop-filter: dy [N,H,W,Cout], x [N,H,W,Cin] -> dw [k,k,Cin,Cout] (accumulated into out)."""

@@ -142,6 +142,12 @@ def lib() -> C.CDLL:
         "ddl_p2p_latency": ([vp, i32, i32, u32, i32, vp, vp], i32),
         "ddl_p2p_copy": ([vp, vp, i64, i32, vp], i32),
         "ddl_p2p_spin": ([vp, i32, C.c_uint64, vp, vp], i32),
+        "ddl_patch_conv_fits": ([i32, i32, i32, i32], i32),
+        "ddl_patch_conv_preferred": ([i32, i32, i32, i32], i32),
+        "ddl_patch_plan_create": ([i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32], vp),
+        "ddl_patch_plan_run": ([vp, vp], i32),
+        "ddl_patch_plan_destroy": ([vp], None),
+        "ddl_patch_plan_set_trace": ([vp, vp], i32),
         "ddl_async_owner_start": ([C.POINTER(Comm), C.POINTER(SyncArgs), i32, vp, vp, i32, i64, i32, f32, f32, vp], i32),
         "ddl_async_push": ([C.POINTER(Comm), C.POINTER(AsyncArgs), vp], i32),
         "ddl_async_apply": ([C.POINTER(Comm), C.POINTER(SyncArgs), i32, vp, i32, i64, i32, f32, f32, vp], i32),

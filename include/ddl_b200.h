@@ -154,6 +154,19 @@ void ddl_tc_plan_destroy(DdlTcPlan* pl);
 int ddl_tc_plan_info(const DdlTcPlan* pl, int* out8);
 int ddl_tc_plan_needs_zero(const DdlTcPlan* pl);
 
+/* ---- patch-resident 5x5 convolution (csrc/tc_patch.cu): one CTA per image, the zero-padded activation patch is loaded
+ * once and every filter tap reads it through a shifted shared-memory descriptor (conv2d + bias + relu + max_pool2d of
+ * model.py:35-42 and its backprop-input).  dgrad = 0: out [N,ceil(H/2),ceil(W/2),nout], idx nullable; dgrad = 1: out
+ * [N,H,W,nout] = dgrad masked by idx < 4, dbias += column sums.  ddl_patch_conv_fits says whether a shape qualifies. */
+typedef struct DdlPatchPlan DdlPatchPlan;
+int ddl_patch_conv_fits(int H, int W, int cred, int nout);
+int ddl_patch_conv_preferred(int H, int W, int cred, int nout);   /* fits AND >= 70% of its M rows are real pixels */
+DdlPatchPlan* ddl_patch_plan_create(int dgrad, const float* act, const float* w, const float* bias, float* out, uint8_t* idx,
+                                    float* dbias, int N, int H, int W, int cred, int nout);
+int ddl_patch_plan_run(const DdlPatchPlan* pl, cudaStream_t s);
+void ddl_patch_plan_destroy(DdlPatchPlan* pl);
+int ddl_patch_plan_set_trace(DdlPatchPlan* pl, unsigned long long* trace);   /* lab build (ops/build.py --lab) only */
+
 /* ---- allocation-free convolution block (csrc/tc_gemm.cu).  No counterpart in the reference. --------
  * For host programs that must not call cudaMalloc: ones that have given the whole device to another
  * allocator (a caching pool that owns all free memory, an MPS / MIG slice with a hard quota), where a

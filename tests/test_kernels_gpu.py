@@ -216,6 +216,44 @@ def test_tc_dgrad_poolgrad_and_pooled_first_layer_wgrad(B, Cin, ntile, cluster):
     assert rel_err(dw1.squeeze(2).permute(2, 0, 1), wt.grad.squeeze(1).float()) < 1e-3
 
 
+@pytest.mark.parametrize("B,H,Cin,Cout", [(100, 14, 32, 64), (3, 14, 64, 32), (7, 7, 64, 128), (5, 28, 32, 32), (2, 10, 32, 96)])
+def test_patch_resident_conv_forward_and_dgrad(B, H, Cin, Cout):
+    """csrc/tc_patch.cu: the padded activation patch resident in shared memory, 25 taps as shifted descriptors.
+    Forward (+ bias + ReLU + pool) and dgrad (+ ReLU mask of the layer below, pooled layout) against torch in fp64, and
+    against the tap-by-tap plans of tc_gemm.cu."""
+    from ddl_b200.ops import functional as K, native
+    assert native.lib().ddl_patch_conv_fits(H, H, Cin, Cout) == 1
+    torch.manual_seed(21)
+    x = torch.randn(B, H, H, Cin, device=dev())
+    w = torch.randn(5, 5, Cin, Cout, device=dev()) * 0.05
+    bias = torch.randn(Cout, device=dev()) * 0.1
+    to_ref(None)
+    a = F.relu(F.conv2d(x.permute(0, 3, 1, 2).double(), w.permute(3, 2, 0, 1).double(), bias.double(), padding=2))
+    ref = F.max_pool2d(a, 2, 2, ceil_mode=True).permute(0, 2, 3, 1).float()
+    y, idx = K.conv5x5_relu_pool_patch(x, w, bias)
+    assert y.shape == ref.shape and rel_err(y, ref) < TF32_TOL
+    assert torch.equal(idx == 4, y == 0)
+    y2, none = K.conv5x5_relu_pool_patch(x, w, bias, want_idx=False)
+    assert none is None and torch.equal(y2, y)
+    if Cout % 32 == 0 and Cout in (32, 64, 128):
+        y3, idx3 = K.conv5x5_relu_pool(x, w, bias, ntile=min(Cout, 128))
+        assert rel_err(y, y3) < 1e-5
+    # dgrad: dY [B,H,H,Cout] -> gradient wrt the conv input, masked by the ReLU / pool state of the layer below
+    dy = torch.randn(B, H, H, Cout, device=dev())
+    below = torch.randn(B, 2 * H, 2 * H, Cin, device=dev())
+    _, pidx = K.bias_relu_maxpool(below)
+    g, db = K.conv5x5_dgrad_poolgrad_patch(dy, w, pidx)
+    xin = torch.zeros(B, H, H, Cin, device=dev(), dtype=torch.double, requires_grad=True)
+    out = F.conv2d(xin.permute(0, 3, 1, 2), w.double().permute(3, 2, 0, 1), padding=2).permute(0, 2, 3, 1)
+    out.backward(dy.double())
+    want = torch.where(pidx < 4, xin.grad.float(), torch.zeros_like(g))
+    assert rel_err(g, want) < TF32_TOL
+    assert torch.equal(g == 0, (pidx == 4) | (g == 0))
+    assert rel_err(db, want.sum(dim=(0, 1, 2))) < 1e-3
+    g2, none = K.conv5x5_dgrad_poolgrad_patch(dy, w, pidx, want_db=False)
+    assert none is None and torch.equal(g2, g)
+
+
 @pytest.mark.parametrize("H,Cin,Cout", [(14, 32, 64), (7, 64, 128), (4, 128, 256)])
 def test_tc_conv_dgrad_wgrad(H, Cin, Cout):
     from ddl_b200.ops import functional as K

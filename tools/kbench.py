@@ -54,7 +54,29 @@ def case_sync():
     timeit("sync push/update/pull, all buckets (world=1)", lambda: t.step(all_buckets=True))
 
 
-CASES = {"w1pooled": case_w1pooled, "conv1": case_conv1, "sync": case_sync}
+def case_patch():
+    """patch-resident conv (tc_patch.cu) against the tap-by-tap plans (tc_gemm.cu), same layer, plans built once"""
+    import ctypes as C
+    B = 100
+    for (H, Cin, Cout, nt_f, cl_f, nt_d, cl_d) in [(14, 32, 64, 64, 1, 32, 1), (7, 64, 128, 128, 4, 64, 4)]:
+        x = torch.randn(B, H, H, Cin, device=dev); w = torch.randn(5, 5, Cin, Cout, device=dev) * .05; b = torch.randn(Cout, device=dev) * .1
+        PH = (H + 1) // 2
+        y = torch.empty(B, PH, PH, Cout, device=dev); idx = torch.empty(B, PH, PH, Cout, device=dev, dtype=torch.uint8)
+        dy = torch.randn(B, H, H, Cout, device=dev)
+        _, pidx = K.bias_relu_maxpool(torch.randn(B, 2 * H, 2 * H, Cin, device=dev))
+        g = torch.empty(B, H, H, Cin, device=dev); db = torch.zeros(Cin, device=dev)
+        plans = {
+            "tap-by-tap fwd+pool": (L.ddl_tc_plan_conv_pool(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), idx.data_ptr(), B, H, H, Cin, Cout, 5, nt_f, cl_f), L.ddl_tc_plan_run),
+            "patch       fwd+pool": (L.ddl_patch_plan_create(0, x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), idx.data_ptr(), None, B, H, H, Cin, Cout), L.ddl_patch_plan_run),
+            "tap-by-tap dgrad+mask": (L.ddl_tc_plan_dgrad_poolgrad(dy.data_ptr(), w.data_ptr(), pidx.data_ptr(), g.data_ptr(), db.data_ptr(), B, H, H, Cout, Cin, 5, nt_d, cl_d), L.ddl_tc_plan_run),
+            "patch       dgrad+mask": (L.ddl_patch_plan_create(1, dy.data_ptr(), w.data_ptr(), None, g.data_ptr(), pidx.data_ptr(), db.data_ptr(), B, H, H, Cout, Cin), L.ddl_patch_plan_run),
+        }
+        for name, (pl, run) in plans.items():
+            assert pl, native.last_error()
+            timeit("%dx%d %d->%d %s" % (H, H, Cin, Cout, name), lambda: run(pl, native.stream_ptr()))
+
+
+CASES = {"patch": case_patch, "w1pooled": case_w1pooled, "conv1": case_conv1, "sync": case_sync}
 
 if __name__ == "__main__":
     for name in (sys.argv[1:] or list(CASES)):
