@@ -247,6 +247,46 @@ def case_async_dedicated(rank, world, resident):
     tr.transport.close()
 
 
+def case_ckpt_resume(rank, world):
+    """--ckpt-path / --resume through the fused transport: parameters in the reference's names and layouts,
+    Adam m / v gathered from the shard owners, step counts.  A resumed trainer holds bitwise the saved state and takes
+    bitwise the same next step when fed the same gradients."""
+    import tempfile
+    path = os.path.join(tempfile.gettempdir(), "ddl_ckpt_test_%d.pt" % world)
+    cfg = base_cfg(mode="sync", shard="greedy", num_ps=world, num_workers=world, transport="fused", optimizer="adam",
+                   variant="mnist_sync_sharding_greedy", graphs=False)
+    a = SPMDTrainer(cfg, rank, world, rank, "colocated")
+    for i in range(3):
+        a.train_step(i)
+    torch.cuda.synchronize()
+    a.save(path)
+    dist.barrier()
+    blob = torch.load(path, map_location="cpu", weights_only=False)
+    assert sorted(blob["vars"]) == sorted("mnist/v%d" % i for i in range(14)) and blob["t"] == 3 and blob["step"] == 3
+    assert tuple(blob["vars"]["mnist/v2"].shape) == (5, 5, 32, 64) and tuple(blob["vars"]["mnist/v8"].shape) == (1024, 1024)
+    b = SPMDTrainer(cfg.replace(resume=path), rank, world, rank, "colocated")
+    assert torch.equal(a.params.flat, b.params.flat), "resumed parameters differ"
+    assert b.global_step == 3 and b.transport.stats()["optimizer_steps"] == 3
+    for sh in a.layout.my_shards:                                  # optimizer state of the ranges this rank owns
+        lo, hi = a.plan.shard_range[sh]
+        assert torch.equal(a.transport.m[lo:hi], b.transport.m[lo:hi]) and torch.equal(a.transport.v[lo:hi], b.transport.v[lo:hi])
+    gen = torch.Generator(device="cuda").manual_seed(77 + rank)
+    g = torch.randn(a.grads.flat.shape, device="cuda", generator=gen)
+    for t in (a, b):
+        t.grads.flat.copy_(g)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t.transport.begin_step()
+        t.transport.step(all_buckets=True)
+        torch.cuda.synchronize()
+        dist.barrier()
+    assert torch.equal(a.params.flat, b.params.flat), "the step after resume differs"
+    a.transport.close()
+    b.transport.close()
+    if rank == 0:
+        os.remove(path)
+
+
 def main():
     case = sys.argv[1]
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -284,6 +324,8 @@ def main():
     elif case == "async_dedicated":
         case_async_dedicated(rank, world, resident=True)
         case_async_dedicated(rank, world, resident=False)
+    elif case == "ckpt_resume":
+        case_ckpt_resume(rank, world)
     elif case == "async_train":
         case_async_train(rank, world)
     else:

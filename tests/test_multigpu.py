@@ -29,6 +29,6 @@ def run_case(case, nproc=None, timeout=300):
         assert ok, "\n".join([r.stdout[-1500:], keep, "\n".join(lines), err[-1500:]])
 
 
-@pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "sync_vs_nccl", "sync_nvls_off", "sync_nvls_on", "async_sgd", "async_adam", "async_parity", "async_dedicated", "async_train"])
+@pytest.mark.parametrize("case", ["sync_colocated", "sync_dedicated", "sync_vs_nccl", "sync_nvls_off", "sync_nvls_on", "async_sgd", "async_adam", "async_parity", "async_dedicated", "async_train", "ckpt_resume"])
 def test_fused_transport(case):
     run_case(case)
