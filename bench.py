@@ -18,7 +18,8 @@ Numbers printed (one JSON line, rank 0):
                its batch from pinned host memory (H2D) and the host reads the step's loss (D2H).
   --impl reference  - the unmodified reference cannot be installed here (no setup.py; needs
                TensorFlow 1.x + mpi4py + mpiexec, none present) -> {"unavailable": ...}.
-  --impl host_ps / nccl / torch - the stand-in baseline rungs of BASELINE.md section 2.
+  --impl host_ps / nccl / torch / torch_graph - the stand-in baseline rungs of BASELINE.md section 2 (torch_graph: cuDNN /
+               cuBLAS with TF32 + NCCL reduce_scatter / all_gather, the whole step in one CUDA graph).
 """
 from __future__ import annotations
 
@@ -85,7 +86,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "host_ps", "nccl", "torch"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "host_ps", "nccl", "torch", "torch_graph"])
     ap.add_argument("--variant", default="mnist_sync_sharding_greedy")
     ap.add_argument("--shard", default=None)
     ap.add_argument("--width-mult", type=int, default=1)
@@ -218,6 +219,14 @@ def main() -> int:
     if a.impl == "host_ps":
         from baseline.host_ps.bench_host_ps import run as run_host
         return run_host(a, emit)
+    if a.impl == "torch_graph":
+        if int(os.environ.get("WORLD_SIZE", "1")) != a.gpus and a.gpus > 1:
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(a.gpus),
+                   "--master-addr", "127.0.0.1", "--master-port", "29532", os.path.abspath(__file__)] + sys.argv[1:]
+            os.dup2(real_stdout, 1)
+            return subprocess.call(cmd)
+        from baseline.nccl_ps.bench_nccl_ps import run as run_tg
+        return run_tg(a, emit)
 
     import torch
     import torch.distributed as dist
