@@ -88,16 +88,15 @@ def run(a, emit=lambda o: print(json.dumps(o))) -> int:
     y_in = torch.zeros(B, dtype=torch.long, device=dev)
     loss_out = torch.zeros((), device=dev)
 
-    def step():
+    def compute():
         logits = forward(views, x_in, keep)
         loss = F.cross_entropy(logits, y_in)
         gs = torch.autograd.grad(loss, views)
         for gv, gg in zip(gviews, gs):
             gv.copy_(gg)
         loss_out.copy_(loss.detach())
-        if world > 1:
-            mine = grads[my]
-            dist.reduce_scatter_tensor(mine, grads, op=dist.ReduceOp.SUM)       # push + sum: the owner gets its shard
+
+    def update():
         gsh = grads[my]
         t_dev.add_(1.0)                                                          # TF1 Adam: eps outside the bias correction
         lr_t = lr * torch.sqrt(1.0 - b2 ** t_dev) / (1.0 - b1 ** t_dev)
@@ -105,21 +104,49 @@ def run(a, emit=lambda o: print(json.dumps(o))) -> int:
         v.mul_(b2).addcmul_(gsh, gsh, value=1 - b2)
         with torch.no_grad():
             flat[my].sub_(lr_t * m / (v.sqrt() + eps))
-            if world > 1:
-                dist.all_gather_into_tensor(flat, flat[my].clone())            # pull: every worker gets every shard
 
-    # warm-up on a side stream (cuDNN autotune, NCCL channels), then capture the step
+    def push():                                                                  # push + sum: the owner gets its shard
+        dist.reduce_scatter_tensor(grads[my], grads, op=dist.ReduceOp.SUM)
+
+    def pull():                                                                  # pull: every worker gets every shard
+        dist.all_gather_into_tensor(flat, flat[my].clone())
+
+    # warm-up on a side stream (cuDNN autotune, NCCL channels), then capture.  One rank: the whole step is ONE graph.
+    # Several ranks: forward + backward is one graph, the optimizer another, and the two NCCL collectives are issued
+    # between them (4 launches per step; capturing the collectives too hung this image's NCCL 2.28 / torch 2.11 pair).
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(side):
         for i in range(max(3, a.warmup)):
             x_in.copy_(xs[i % nbatch]); y_in.copy_(ys[i % nbatch])
-            step()
+            compute()
+            if world > 1:
+                push()
+            update()
+            if world > 1:
+                pull()
     torch.cuda.current_stream().wait_stream(side)
     torch.cuda.synchronize()
-    graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(graph):
-        step()
+    g_compute, g_update = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    if world == 1:
+        with torch.cuda.graph(g_compute):
+            compute()
+            update()
+    else:
+        with torch.cuda.graph(g_compute):
+            compute()
+        with torch.cuda.graph(g_update):
+            update()
+
+    class _Step:
+        @staticmethod
+        def replay():
+            g_compute.replay()
+            if world > 1:
+                push()
+                g_update.replay()
+                pull()
+    graph = _Step
 
     def sync_all():
         torch.cuda.synchronize()
@@ -151,7 +178,7 @@ def run(a, emit=lambda o: print(json.dumps(o))) -> int:
               "dtype": "tf32 allowed (cuDNN / cuBLAS), fp32 storage", "data": "synthetic MNIST-shaped, random-init weights",
               "config": {"model": "mnist_cnn_14var" + ("" if a.width_mult == 1 else "_x%d" % a.width_mult),
                          "params": sum(sizes), "global_batch": B * world, "batch_per_worker": B, "optimizer": "adam (TF1 formula)",
-                         "parallelism": "flat shards, NCCL reduce_scatter + all_gather, whole step in one CUDA graph",
+                         "parallelism": "flat shards, NCCL reduce_scatter + all_gather; " + ("whole step in one CUDA graph" if world == 1 else "two CUDA graphs (fwd+bwd, optimizer) around the two collectives"),
                          "cuda_graph": True, "l2": "256 MiB written between timed steps"},
               "first_loss": first, "final_loss": float(loss_out)})
     if world > 1:
