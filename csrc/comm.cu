@@ -718,12 +718,12 @@ int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, 
   }
   int grid = comm_grid(elems);
   // a bucket that overlaps the backward shares the SMs with the GEMM kernels of the critical chain: keep it narrow
-  static const int cap = getenv("DDL_COMM_CAP") ? atoi(getenv("DDL_COMM_CAP")) : 592;
+  static const int cap = DDL_LAB_ENV("DDL_COMM_CAP") ? atoi(DDL_LAB_ENV("DDL_COMM_CAP")) : 592;
   const bool overlapped = a->nbuckets > 1 && a->bucket < a->nbuckets - 1;
   if (overlapped && grid > cap) grid = cap;
   // bandwidth-bound ranges (>= 16 float4 per thread at the chosen grid): 4 float4 per thread per trip; smaller
   // ranges are latency-bound, and multimem loads measured faster with one (profiles/comm_roofline.md)
-  static const int force_u = getenv("DDL_COMM_UNROLL") ? atoi(getenv("DDL_COMM_UNROLL")) : 0;
+  static const int force_u = DDL_LAB_ENV("DDL_COMM_UNROLL") ? atoi(DDL_LAB_ENV("DDL_COMM_UNROLL")) : 0;
   const bool wide = force_u ? force_u > 1 : (c->mc_grads == nullptr && elems / 4 >= (int64_t)grid * kCommThreads * 16);
   int skip_a = 0;
   if (overlapped && c->world > 1) {

@@ -9,6 +9,7 @@
 #include <cuda.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 // ------------------------------------------------------------------------------------ errors
 namespace ddl {
@@ -34,6 +35,15 @@ const char* get_error();
   } while (0)
 
 #define DDL_LAUNCH_CHECK() DDL_CHECK_CUDA(cudaGetLastError())
+
+// Planning / scheduling experiment switches (tile shapes, ring depths, split policies, ...) are read from the environment
+// only in the lab build (python -m ddl_b200.ops.build --lab, used by the sweeps under tools/); the product library always
+// takes the measured defaults.  Product switches are the documented ones: DDL_PDL, DDL_WAIT_TIMEOUT_NS (compile time).
+#ifdef DDL_TC_LAB
+#define DDL_LAB_ENV(name) getenv(name)
+#else
+#define DDL_LAB_ENV(name) (static_cast<const char*>(nullptr))
+#endif
 
 namespace ddl {
 bool pdl_enabled();        // DDL_PDL=0 disables programmatic dependent launch

@@ -133,13 +133,13 @@ void pick_staged_tiling(int pix_tiles, int nout, int kiters, int* ntile, int* cl
     }
   }
   if (best_nt == 0) best_nt = 32;
-  if (getenv("DDL_POOL_NT") && nout % atoi(getenv("DDL_POOL_NT")) == 0) best_nt = atoi(getenv("DDL_POOL_NT"));
-  if (getenv("DDL_POOL_CL")) best_cl = atoi(getenv("DDL_POOL_CL"));
+  if (DDL_LAB_ENV("DDL_POOL_NT") && nout % atoi(DDL_LAB_ENV("DDL_POOL_NT")) == 0) best_nt = atoi(DDL_LAB_ENV("DDL_POOL_NT"));
+  if (DDL_LAB_ENV("DDL_POOL_CL")) best_cl = atoi(DDL_LAB_ENV("DDL_POOL_CL"));
   *ntile = best_nt; *cluster = best_cl;
 }
 
 bool fuse_pool_enabled() {
-  static const bool on = getenv("DDL_NO_POOL_FUSE") == nullptr;
+  static const bool on = DDL_LAB_ENV("DDL_NO_POOL_FUSE") == nullptr;
   return on;
 }
 
@@ -269,7 +269,7 @@ int build_bwd(DdlEngine* e) {
         // beside conv2's wgrad, whose CTAs take whole SMs; one patch CTA per image also needs a whole SM each
         // (208 KB), so 12 of the 100 wait for a second wave, while the tap-by-tap plan's 100 KB CTAs pack two per SM
         // into what is free.  Kept for DDL_PATCH_DGRAD=1 experiments.
-        static const bool patch_dgrad = getenv("DDL_PATCH_DGRAD") != nullptr;
+        static const bool patch_dgrad = DDL_LAB_ENV("DDL_PATCH_DGRAD") != nullptr;
         if (patch_dgrad && e->w1_pooled && ddl_patch_conv_preferred(S, S, cout, cin)) {
           e->pdg_conv0 = ddl_patch_plan_create(1, e->dfull[1], e->P(v), nullptr, e->dpool[0], e->idx[0], e->G(1), B, S, S, cout, cin);
           if (!e->pdg_conv0) return -1;
@@ -439,7 +439,7 @@ int ddl_engine_train_step(DdlEngine* e, const float* x, const int* y, cudaStream
   const int vf = 2 * e->nconv;
   // fc3 forward + loss + fc3 backward in one cluster kernel (also emits the fc2 bias gradient = column sums of dh2);
   // DDL_FC3_SPLIT=1 or a shape that does not fit: the two separate kernels
-  static const bool fc3_split = getenv("DDL_FC3_SPLIT") != nullptr;
+  static const bool fc3_split = DDL_LAB_ENV("DDL_FC3_SPLIT") != nullptr;
   if (!fc3_split && ddl_fc3_fused_fits(B, e->F[2], e->F[3])) {
     if (ddl_fc3_fused_st(e->h2, e->P(vf + 4), e->P(vf + 5), y, e->G(vf + 4), e->G(vf + 5), e->dh2, e->G(vf + 3), c.st, B,
                          e->F[2], e->F[3], 1.f / (float)B, 1, c.keep_prob, s)) return -1;

@@ -1019,8 +1019,8 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   //    fusion and needs no zeroing, but rank 0 alone reads (ksplit-1) tiles: 44.5 us for the same conv4
   //    case, so it is only used where the tile is narrow (N tile 32) and the epilogue must stay fused.
   const bool fused_epi = (flags & (EPI_BIAS | EPI_RELU | EPI_DROPOUT | EPI_MASKPOS)) != 0 || colsum != nullptr;
-  const bool want_cluster = po != nullptr || (getenv("DDL_TC_NO_CLUSTER") == nullptr &&
-                                             (fused_epi || getenv("DDL_TC_FORCE_CLUSTER") != nullptr));
+  const bool want_cluster = po != nullptr || (DDL_LAB_ENV("DDL_TC_NO_CLUSTER") == nullptr &&
+                                             (fused_epi || DDL_LAB_ENV("DDL_TC_FORCE_CLUSTER") != nullptr));
   if (po && p.ksplit != (ksplit < 1 ? 1 : ksplit)) return (delete pl, fail("staged epilogue: split exceeds the k iterations"));
   if (want_cluster && p.ksplit > 8) p.ksplit = 8;
   p.cluster = (want_cluster && p.ksplit > 1) ? p.ksplit : 1;
@@ -1031,7 +1031,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   // K4 pull plans and cluster sizes that do not divide the tile into multiples of 4 columns.
   const bool staged_gen = !po && p.cluster > 1 && fused_epi && !(w_store_dst != nullptr && !dgrad && w_store_dst != w) &&
                           (p.cluster == 2 || p.cluster == 4 || p.cluster == 8) && ntile % p.cluster == 0 &&
-                          (ntile / p.cluster) % 4 == 0 && getenv("DDL_TC_LEADER_EPI") == nullptr;
+                          (ntile / p.cluster) % 4 == 0 && DDL_LAB_ENV("DDL_TC_LEADER_EPI") == nullptr;
   if (staged_gen) p.flags |= EPI_STAGED;
   p.pool_out = po ? po->out2 : nullptr;
   p.pool_idx = po ? po->idx : nullptr;
@@ -1041,8 +1041,8 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   p.debug = 0;
   p.trace = nullptr;
 #ifdef DDL_TC_LAB
-  p.debug = getenv("DDL_TC_DEBUG") ? atoi(getenv("DDL_TC_DEBUG")) : 0;
-  if (getenv("DDL_TC_TRACE")) {
+  p.debug = DDL_LAB_ENV("DDL_TC_DEBUG") ? atoi(DDL_LAB_ENV("DDL_TC_DEBUG")) : 0;
+  if (DDL_LAB_ENV("DDL_TC_TRACE")) {
     if (cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long)) != cudaSuccess) { delete pl; return fail("cudaMalloc(trace) failed"); }
     cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
   }
@@ -1060,7 +1060,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   // write-through warp, which walks single blocks).
   const int per_cta_blocks = ceil_div(p.kiters, p.ksplit);
   p.kps = 1;
-  if (getenv("DDL_TC_KPS") && !p.pull && per_cta_blocks >= 4) p.kps = atoi(getenv("DDL_TC_KPS")) >= 2 ? 2 : 1;
+  if (DDL_LAB_ENV("DDL_TC_KPS") && !p.pull && per_cta_blocks >= 4) p.kps = atoi(DDL_LAB_ENV("DDL_TC_KPS")) >= 2 ? 2 : 1;
   const int stage_bytes = p.kps * (kTileM * 128 + ntile * 128);
   // <= ~110 KB of stages: two CTAs per SM stay resident (grids of 150-300 CTAs run as one wave) and
   // 4 stages already cover the ~1000-cycle TMA latency at ~600 cycles per k-iteration
@@ -1069,7 +1069,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   if (stages > kMaxStages) stages = kMaxStages;
   const int fills = ceil_div(per_cta_blocks, p.kps);           // stage fills per CTA
   if (stages > fills) stages = fills < 2 ? 2 : fills;
-  if (getenv("DDL_TC_STAGES")) stages = atoi(getenv("DDL_TC_STAGES"));
+  if (DDL_LAB_ENV("DDL_TC_STAGES")) stages = atoi(DDL_LAB_ENV("DDL_TC_STAGES"));
   // staged epilogues reuse the stage memory: D (cluster > 1: ntile x 128 floats) + S (128 x (cw + 1) floats)
   size_t epi_bytes = 0;
   if (po || (p.flags & EPI_STAGED)) {
@@ -1179,10 +1179,10 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   // boxes per stage (deeper pipeline, larger pixel boxes) and a narrower red.add epilogue per CTA.
   // ... but inside the training step the wider grids take SMs from the critical dgrad chain running next to them
   // (336k vs 367k samples/s), so it is opt-in: DDL_WGRAD_POLICY=wave
-  static const bool old_policy = !(getenv("DDL_WGRAD_POLICY") && !strcmp(getenv("DDL_WGRAD_POLICY"), "wave"));
+  static const bool old_policy = !(DDL_LAB_ENV("DDL_WGRAD_POLICY") && !strcmp(DDL_LAB_ENV("DDL_WGRAD_POLICY"), "wave"));
   if (!old_policy && tpc_max > 5) tpc_max = 5;
-  if (getenv("DDL_WGRAD_TPC") && atoi(getenv("DDL_WGRAD_TPC")) >= 1 && atoi(getenv("DDL_WGRAD_TPC")) < tpc_max)
-    tpc_max = atoi(getenv("DDL_WGRAD_TPC"));
+  if (DDL_LAB_ENV("DDL_WGRAD_TPC") && atoi(DDL_LAB_ENV("DDL_WGRAD_TPC")) >= 1 && atoi(DDL_LAB_ENV("DDL_WGRAD_TPC")) < tpc_max)
+    tpc_max = atoi(DDL_LAB_ENV("DDL_WGRAD_TPC"));
   if (tpc_max > taps) tpc_max = taps;
   p.tgroups = ceil_div(taps, tpc_max);
   p.tpc = ceil_div(taps, p.tgroups);
@@ -1192,7 +1192,7 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   const int boxes = p.a_alloc + p.tpc * b_boxes;
   // rows per stage: multiple of 8 (one UMMA K step = 8 pixel rows); two stages must fit in shared memory.
   // DDL_WGRAD_SMEM_KB (perf experiments): shared-memory budget of a wgrad CTA (default 216: one CTA per SM)
-  static const int smem_kb = getenv("DDL_WGRAD_SMEM_KB") ? atoi(getenv("DDL_WGRAD_SMEM_KB")) : 216;
+  static const int smem_kb = DDL_LAB_ENV("DDL_WGRAD_SMEM_KB") ? atoi(DDL_LAB_ENV("DDL_WGRAD_SMEM_KB")) : 216;
   int max_rows = ((smem_kb * 1024 / 2) / (boxes * 128)) & ~7;
   if (max_rows > 128) max_rows = 128;
   if (max_rows < 8) { delete pl; return fail("tap group does not fit in shared memory"); }
@@ -1226,7 +1226,7 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   p.out = out;
   p.trace = nullptr;
 #ifdef DDL_TC_LAB
-  if (getenv("DDL_TC_TRACE")) {
+  if (DDL_LAB_ENV("DDL_TC_TRACE")) {
     if (cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long)) != cudaSuccess) { delete pl; return fail("cudaMalloc(trace) failed"); }
     cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
   }

@@ -513,7 +513,7 @@ DdlPatchPlan* ddl_patch_plan_create(int dgrad, const float* act, const float* w,
   p.trace = nullptr;
   p.debug = 0;
 #ifdef DDL_TC_LAB
-  p.debug = getenv("DDL_PATCH_DEBUG") ? atoi(getenv("DDL_PATCH_DEBUG")) : 0;
+  p.debug = DDL_LAB_ENV("DDL_PATCH_DEBUG") ? atoi(DDL_LAB_ENV("DDL_PATCH_DEBUG")) : 0;
 #endif
   pl->grid = dim3(N, 1, 1);
   const uint64_t da[4] = {(uint64_t)cred, (uint64_t)W, (uint64_t)H, (uint64_t)N};

@@ -98,3 +98,6 @@ def build(force: bool = False, verbose: bool = False, lab: bool = False) -> str:
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, lab="--lab" in sys.argv))
+    if "--sass" in sys.argv or "-v" in sys.argv:
+        # per-kernel SASS evidence (profiles/sass/*.txt, profiles/sass_evidence.md), regenerated from the library just built
+        subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "sass_extract.py")])

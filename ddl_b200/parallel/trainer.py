@@ -203,12 +203,7 @@ class SPMDTrainer:
         for slot in range(nslots):
             l0 = native.launches()
             g = torch.cuda.CUDAGraph()
-            # the main stream of the capture carries the critical chain (forward, dgrads); the engine's side streams
-            # (wgrads, overlapped push) have the lowest priority, so a higher-priority capture stream lets the
-            # chain's CTAs win SMs whenever both are pending
-            prio = int(os.environ.get("DDL_CAPTURE_PRIO", "0"))
-            cap = torch.cuda.Stream(device=self.device, priority=prio) if prio else None
-            with (torch.cuda.graph(g, stream=cap) if cap is not None else torch.cuda.graph(g)):
+            with torch.cuda.graph(g):
                 self.transport.begin_step(**self._begin_kw)
                 if lay.is_worker:
                     self.model.impl.enqueue_train_step(self._x_slot[slot], self._y_slot[slot])

@@ -82,3 +82,18 @@ def test_fc3_fused_kernel_shape_limits():
     assert L.ddl_fc3_fused_fits(257, 512, 10) == 0      # one row per warp: at most 32 x 8 rows
     assert L.ddl_fc3_fused_fits(100, 3072, 10) == 0     # k-slice of a CTA is at most 256 columns
     assert L.ddl_fc3_fused_fits(100, 510, 10) == 0      # K % 4
+
+
+def test_committed_sass_evidence_belongs_to_the_sources_in_the_tree():
+    """profiles/sass_evidence.md and profiles/sass/*.txt are generated from the built library (tools/sass_extract.py, also
+    run by ``python -m ddl_b200.ops.build -v``); the digest they quote must be the digest of the sources as they are now."""
+    import os, re
+    from ddl_b200.ops import build
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "profiles", "sass_evidence.md")).read()
+    m = re.search(r"Library source digest: `([0-9a-f]{64})`", text)
+    assert m, "no digest in profiles/sass_evidence.md"
+    assert m.group(1) == build._digest(), "profiles/sass* are stale: run python tools/sass_extract.py"
+    for name in ("tc_act_gemm_kernel", "tc_wgrad_kernel", "tc_patch_conv_kernel"):
+        listing = open(os.path.join(root, "profiles", "sass", name + ".txt")).read()
+        assert "UTCHMMA" in listing and "UTMALDG" in listing and m.group(1) in listing
