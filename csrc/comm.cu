@@ -76,6 +76,17 @@ DDL_DEVICE void pad_wait(const DdlComm& c, uint32_t base, uint32_t epoch) {
   }
 }
 
+// Consume 16 bytes of a worker's accumulator plane: read, then subtract exactly what was read with ONE vector red.add.
+// The pushes counted by the snapshot have fully landed (their counter bump is release-ordered behind their reds), so the
+// value read holds all of them; adds of a LATER push that race with this survive the subtraction (x + a - x), which is what
+// "every push applied exactly once" needs - four scalar atomicExch per float4 did the same at 4x the atomic traffic
+// (61 us for the apply of a 2.66 M parameter shard, profiles/ncu_full_r2_step_summary.csv).
+DDL_DEVICE float4 take_plane(float* pl) {
+  const float4 g = __ldcg(reinterpret_cast<const float4*>(pl));
+  if (g.x != 0.f || g.y != 0.f || g.z != 0.f || g.w != 0.f) red_add_v4_f32(pl, make_float4(-g.x, -g.y, -g.z, -g.w));
+  return g;
+}
+
 // optimizer arithmetic on registers: returns the new parameters, updates mv / vv in place
 template <int KIND>
 DDL_DEVICE float4 opt_math(float4 pv, float4 gv, float4& mv, float4& vv, float step, float a, float b, float eps) {
@@ -394,8 +405,7 @@ async_apply_kernel(const DdlComm c, const DdlSyncArgs a, const DdlAsyncState* as
       g[w] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (w < nworkers && ((mask >> w) & 1u)) {
         float* pl = acc + (int64_t)w * slot_stride + i;
-        g[w].x = atomicExch(pl, 0.f); g[w].y = atomicExch(pl + 1, 0.f);
-        g[w].z = atomicExch(pl + 2, 0.f); g[w].w = atomicExch(pl + 3, 0.f);
+        g[w] = take_plane(pl);
       }
     }
     if (fold) {
@@ -511,8 +521,7 @@ async_owner_resident_kernel(const DdlComm c, const DdlSyncArgs a, DdlAsyncState*
       for (int w = 0; w < nworkers; ++w) {
         if (!((mask >> w) & 1u)) continue;
         float* pl = acc + (int64_t)w * slot_stride + i;
-        float4 g;
-        g.x = atomicExch(pl, 0.f); g.y = atomicExch(pl + 1, 0.f); g.z = atomicExch(pl + 2, 0.f); g.w = atomicExch(pl + 3, 0.f);
+        float4 g = take_plane(pl);
         if (fold) { gs.x += g.x; gs.y += g.y; gs.z += g.z; gs.w += g.w; continue; }
         g.x *= a.gscale; g.y *= a.gscale; g.z *= a.gscale; g.w *= a.gscale;
         pv = opt_math<KIND>(pv, g, mv, vv, KIND == 2 ? as->lr_t[k] : a.lr, a.a, a.b, a.eps);
@@ -718,12 +727,12 @@ int ddl_sync_push_update_pull(const DdlComm* c, const DdlSyncArgs* a, int kind, 
   }
   int grid = comm_grid(elems);
   // a bucket that overlaps the backward shares the SMs with the GEMM kernels of the critical chain: keep it narrow
-  static const int cap = DDL_LAB_ENV("DDL_COMM_CAP") ? atoi(DDL_LAB_ENV("DDL_COMM_CAP")) : 592;
+  static const int cap = ddl_lab_int("DDL_COMM_CAP", 592);
   const bool overlapped = a->nbuckets > 1 && a->bucket < a->nbuckets - 1;
   if (overlapped && grid > cap) grid = cap;
   // bandwidth-bound ranges (>= 16 float4 per thread at the chosen grid): 4 float4 per thread per trip; smaller
   // ranges are latency-bound, and multimem loads measured faster with one (profiles/comm_roofline.md)
-  static const int force_u = DDL_LAB_ENV("DDL_COMM_UNROLL") ? atoi(DDL_LAB_ENV("DDL_COMM_UNROLL")) : 0;
+  static const int force_u = ddl_lab_int("DDL_COMM_UNROLL", 0);
   const bool wide = force_u ? force_u > 1 : (c->mc_grads == nullptr && elems / 4 >= (int64_t)grid * kCommThreads * 16);
   int skip_a = 0;
   if (overlapped && c->world > 1) {

@@ -41,8 +41,10 @@ const char* get_error();
 // takes the measured defaults.  Product switches are the documented ones: DDL_PDL, DDL_WAIT_TIMEOUT_NS (compile time).
 #ifdef DDL_TC_LAB
 #define DDL_LAB_ENV(name) getenv(name)
+inline int ddl_lab_int(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 #else
 #define DDL_LAB_ENV(name) (static_cast<const char*>(nullptr))
+inline int ddl_lab_int(const char*, int dflt) { return dflt; }
 #endif
 
 namespace ddl {

@@ -133,8 +133,9 @@ void pick_staged_tiling(int pix_tiles, int nout, int kiters, int* ntile, int* cl
     }
   }
   if (best_nt == 0) best_nt = 32;
-  if (DDL_LAB_ENV("DDL_POOL_NT") && nout % atoi(DDL_LAB_ENV("DDL_POOL_NT")) == 0) best_nt = atoi(DDL_LAB_ENV("DDL_POOL_NT"));
-  if (DDL_LAB_ENV("DDL_POOL_CL")) best_cl = atoi(DDL_LAB_ENV("DDL_POOL_CL"));
+  const int lab_nt = ddl_lab_int("DDL_POOL_NT", 0), lab_cl = ddl_lab_int("DDL_POOL_CL", 0);
+  if (lab_nt > 0 && nout % lab_nt == 0) best_nt = lab_nt;
+  if (lab_cl > 0) best_cl = lab_cl;
   *ntile = best_nt; *cluster = best_cl;
 }
 

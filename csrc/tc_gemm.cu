@@ -1041,7 +1041,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   p.debug = 0;
   p.trace = nullptr;
 #ifdef DDL_TC_LAB
-  p.debug = DDL_LAB_ENV("DDL_TC_DEBUG") ? atoi(DDL_LAB_ENV("DDL_TC_DEBUG")) : 0;
+  p.debug = ddl_lab_int("DDL_TC_DEBUG", 0);
   if (DDL_LAB_ENV("DDL_TC_TRACE")) {
     if (cudaMalloc((void**)&p.trace, 512 * 4 * sizeof(unsigned long long)) != cudaSuccess) { delete pl; return fail("cudaMalloc(trace) failed"); }
     cudaMemset(p.trace, 0, 512 * 4 * sizeof(unsigned long long));
@@ -1060,7 +1060,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   // write-through warp, which walks single blocks).
   const int per_cta_blocks = ceil_div(p.kiters, p.ksplit);
   p.kps = 1;
-  if (DDL_LAB_ENV("DDL_TC_KPS") && !p.pull && per_cta_blocks >= 4) p.kps = atoi(DDL_LAB_ENV("DDL_TC_KPS")) >= 2 ? 2 : 1;
+  if (ddl_lab_int("DDL_TC_KPS", 1) >= 2 && !p.pull && per_cta_blocks >= 4) p.kps = 2;
   const int stage_bytes = p.kps * (kTileM * 128 + ntile * 128);
   // <= ~110 KB of stages: two CTAs per SM stay resident (grids of 150-300 CTAs run as one wave) and
   // 4 stages already cover the ~1000-cycle TMA latency at ~600 cycles per k-iteration
@@ -1069,7 +1069,7 @@ static DdlTcPlan* plan_act_impl(int dgrad, const float* act, const float* w, flo
   if (stages > kMaxStages) stages = kMaxStages;
   const int fills = ceil_div(per_cta_blocks, p.kps);           // stage fills per CTA
   if (stages > fills) stages = fills < 2 ? 2 : fills;
-  if (DDL_LAB_ENV("DDL_TC_STAGES")) stages = atoi(DDL_LAB_ENV("DDL_TC_STAGES"));
+  if (ddl_lab_int("DDL_TC_STAGES", 0) > 0) stages = ddl_lab_int("DDL_TC_STAGES", 0);
   // staged epilogues reuse the stage memory: D (cluster > 1: ntile x 128 floats) + S (128 x (cw + 1) floats)
   size_t epi_bytes = 0;
   if (po || (p.flags & EPI_STAGED)) {
@@ -1178,11 +1178,10 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   // fastest split for all three conv layers (20-25 us alone vs 31-45 us with the widest tap groups): fewer shifted X
   // boxes per stage (deeper pipeline, larger pixel boxes) and a narrower red.add epilogue per CTA.
   // ... but inside the training step the wider grids take SMs from the critical dgrad chain running next to them
-  // (336k vs 367k samples/s), so it is opt-in: DDL_WGRAD_POLICY=wave
-  static const bool old_policy = !(DDL_LAB_ENV("DDL_WGRAD_POLICY") && !strcmp(DDL_LAB_ENV("DDL_WGRAD_POLICY"), "wave"));
+  // (336k vs 367k samples/s), so it is a lab-build switch: DDL_WGRAD_POLICY_WAVE=1
+  static const bool old_policy = ddl_lab_int("DDL_WGRAD_POLICY_WAVE", 0) == 0;
   if (!old_policy && tpc_max > 5) tpc_max = 5;
-  if (DDL_LAB_ENV("DDL_WGRAD_TPC") && atoi(DDL_LAB_ENV("DDL_WGRAD_TPC")) >= 1 && atoi(DDL_LAB_ENV("DDL_WGRAD_TPC")) < tpc_max)
-    tpc_max = atoi(DDL_LAB_ENV("DDL_WGRAD_TPC"));
+  if (ddl_lab_int("DDL_WGRAD_TPC", 0) >= 1 && ddl_lab_int("DDL_WGRAD_TPC", 0) < tpc_max) tpc_max = ddl_lab_int("DDL_WGRAD_TPC", 0);
   if (tpc_max > taps) tpc_max = taps;
   p.tgroups = ceil_div(taps, tpc_max);
   p.tpc = ceil_div(taps, p.tgroups);
@@ -1192,7 +1191,7 @@ DdlTcPlan* ddl_tc_plan_wgrad(const float* g, const float* x, float* out, int N, 
   const int boxes = p.a_alloc + p.tpc * b_boxes;
   // rows per stage: multiple of 8 (one UMMA K step = 8 pixel rows); two stages must fit in shared memory.
   // DDL_WGRAD_SMEM_KB (perf experiments): shared-memory budget of a wgrad CTA (default 216: one CTA per SM)
-  static const int smem_kb = DDL_LAB_ENV("DDL_WGRAD_SMEM_KB") ? atoi(DDL_LAB_ENV("DDL_WGRAD_SMEM_KB")) : 216;
+  static const int smem_kb = ddl_lab_int("DDL_WGRAD_SMEM_KB", 216);
   int max_rows = ((smem_kb * 1024 / 2) / (boxes * 128)) & ~7;
   if (max_rows > 128) max_rows = 128;
   if (max_rows < 8) { delete pl; return fail("tap group does not fit in shared memory"); }

@@ -121,7 +121,6 @@ tc_patch_conv_kernel(const __grid_constant__ CUtensorMap map_act, const __grid_c
   const int b_bytes = p.nout * 128;                       // one (tap, channel block) weight tile
   const int stage_bytes = p.tps * p.cblocks * b_bytes;
   const int nstage = 25 / p.tps;                          // ring fills per image
-  const int taps = 25;
   const uint32_t ncols = tmem_cols_pow2(p.tiles * p.nout);
 
   if (threadIdx.x == 0) {
@@ -513,7 +512,7 @@ DdlPatchPlan* ddl_patch_plan_create(int dgrad, const float* act, const float* w,
   p.trace = nullptr;
   p.debug = 0;
 #ifdef DDL_TC_LAB
-  p.debug = DDL_LAB_ENV("DDL_PATCH_DEBUG") ? atoi(DDL_LAB_ENV("DDL_PATCH_DEBUG")) : 0;
+  p.debug = ddl_lab_int("DDL_PATCH_DEBUG", 0);
 #endif
   pl->grid = dim3(N, 1, 1);
   const uint64_t da[4] = {(uint64_t)cred, (uint64_t)W, (uint64_t)H, (uint64_t)N};
