@@ -21,6 +21,11 @@ def run_variant(variant, P, W, extra, timeout=240):
     env = dict(os.environ, OMP_NUM_THREADS="2", DDL_LAUNCH_TIMEOUT=str(timeout))
     cmd = ["bash", os.path.join(ROOT, variant, "run.sh"), str(P), str(W)] + COMMON + extra
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout + 30, env=env)
+    if r.returncode != 0:
+        # one retry: the job is 3+ OS processes meeting on a TCP port picked a moment earlier; on a loaded box the
+        # rendezvous can lose that race (seen once in ~10 suite runs).  A deterministic failure fails twice.
+        print("first attempt failed:\n" + (r.stdout + r.stderr)[-2000:])
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout + 30, env=env)
     assert r.returncode == 0, r.stdout + r.stderr
     return r.stdout
 
