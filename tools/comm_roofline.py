@@ -1,15 +1,28 @@
 """Roofline position of the fused push / update / pull kernels (torchrun, >= 2 ranks).
 
 Times transport-only steps (gradient arenas pre-filled, no model compute) with CUDA events, max over ranks,
-and compares the bytes each rank must move over NVLink with the measured 770 GB/s per direction."""
+and compares the bytes each rank must move over NVLink with the MEASURED link rate: `copy_kernel_gbs_bidir` of
+profiles/nvlink_peak_n<W>.json (tools/p2p_probe.py: a copy kernel reading a peer's buffer while the peer reads
+ours - every rank of these kernels loads both directions at once).  2 ranks: 638.6 GB/s, 8 ranks: 640.1 GB/s per direction."""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.distributed as dist
 from ddl_b200.config import Config
 from ddl_b200.parallel.trainer import SPMDTrainer
 
-LINK_GBS = 770.0
-HBM_GBS = 6546.9
+HBM_GBS = 6546.9                 # MEASURED_PEAKS.json hbm copy bandwidth
+
+
+def link_gbs(world):
+    """per-direction NVLink rate with both directions loaded, from the probe's file for this rank count (else the
+    nearest smaller one); the file name is reported in every output line"""
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles")
+    for name in ("nvlink_peak_n%d.json" % world, os.path.join("r2_8gpu", "nvlink_peak_n%d.json" % world),
+                 "nvlink_peak_n4.json", "nvlink_peak_n2.json"):
+        path = os.path.join(root, name)
+        if os.path.exists(path):
+            return float(json.load(open(path))["copy_kernel_gbs_bidir"]), name
+    raise SystemExit("run tools/p2p_probe.py first: no profiles/nvlink_peak_n*.json")
 
 
 def timed(fn, reps=10):
@@ -32,6 +45,7 @@ def main():
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     wm = int(os.environ.get("WM", "6"))
+    LINK_GBS, link_src = link_gbs(world)
     out = []
     cases = (("sync", "flat", "auto"), ("sync", "flat", "off"), ("async", "flat", "off"))
     if os.environ.get("CASES"):
@@ -76,7 +90,7 @@ def main():
             floor_ms = link_in / (LINK_GBS * 1e6) + shard_bytes * 7 / (HBM_GBS * 1e6)
         rec = {"unroll": os.environ.get("DDL_COMM_UNROLL", "auto"), "cap": os.environ.get("DDL_COMM_CAP", "148"), "mode": mode, "shard": shard, "nvls": bool(getattr(t, "nvls", False)), "world": world,
                "arena_MB": round(n_bytes / 1e6, 1), "ms": round(ms, 4), "roofline_ms": round(floor_ms, 4),
-               "fraction_of_roofline": round(floor_ms / ms, 3),
+               "fraction_of_roofline": round(floor_ms / ms, 3), "link_GBs_floor": LINK_GBS, "link_source": link_src,
                "link_GBs_achieved_per_direction": round(max(link_in, link_out) / ms / 1e6, 1)}
         out.append(rec)
         if rank == 0:
