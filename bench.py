@@ -18,7 +18,7 @@ Numbers printed (one JSON line, rank 0):
                its batch from pinned host memory (H2D) and the host reads the step's loss (D2H).
   --impl reference  - the unmodified reference cannot be installed here (no setup.py; needs
                TensorFlow 1.x + mpi4py + mpiexec, none present) -> {"unavailable": ...}.
-  --impl host_ps / nccl / torch / torch_graph - the stand-in baseline rungs of BASELINE.md section 2 (torch_graph: cuDNN /
+  --impl host_ps / nccl / torch / torch_graph / oracle_cpu - the stand-in baseline rungs of BASELINE.md section 2 (torch_graph: cuDNN /
                cuBLAS with TF32 + NCCL reduce_scatter / all_gather, the whole step in one CUDA graph).
 """
 from __future__ import annotations
@@ -86,7 +86,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "host_ps", "nccl", "torch", "torch_graph"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "host_ps", "nccl", "torch", "torch_graph", "oracle_cpu"])
     ap.add_argument("--variant", default="mnist_sync_sharding_greedy")
     ap.add_argument("--shard", default=None)
     ap.add_argument("--width-mult", type=int, default=1)
@@ -202,6 +202,43 @@ def exposed_push_pull(cfg, a, local, world, ms_step, sync_all, torch, dist, dev,
     return {"exposed_push_pull_ms": ms_step - ms_local, "local_only_ms_per_step": ms_local}
 
 
+def run_oracle_cpu(a, emit) -> int:
+    """The timed CPU baseline of BASELINE.md section 2: the fp32 restatement of the reference's model math
+    (ddl_b200/models/oracle.py: /root/reference/mnist_sync/model/model.py:17-112 in torch CPU ops) + TF1-Adam per
+    variable, one process, host wall clock.  Same model, batch and synthetic data shape as the GPU arms; no GPU, none
+    of the native kernels."""
+    import time
+    import torch
+    from ddl_b200.models import oracle
+    from ddl_b200.models.spec import make_spec
+    spec = make_spec("cnn", a.width_mult)
+    B = a.batch_size
+    g = torch.Generator().manual_seed(1234)
+    ps = oracle.init_params(spec, 1234)
+    opts = [oracle.OracleOptimizer(p, "adam", 1e-4) for p in ps]
+    nb = 16
+    xs = torch.rand(nb, B, 784, generator=g)
+    ys = torch.randint(0, 10, (nb, B), generator=g)
+    warm = max(3, a.warmup)
+    t0, first, loss = 0.0, None, None
+    for i in range(warm + a.steps):
+        if i == warm:
+            t0 = time.perf_counter()
+        loss, grads, _ = oracle.loss_and_grads(ps, xs[i % nb], ys[i % nb], spec, 0.5, None, 1234, i)
+        for p_, g_, o in zip(ps, grads, opts):
+            o.step(p_, g_)
+        first = float(loss) if first is None else first
+    dt = time.perf_counter() - t0
+    emit({"metric": "samples/sec", "value": a.steps * B / dt, "unit": "samples/s", "n_gpus": 0, "steps": a.steps,
+          "warmup": warm, "ms_per_step": dt * 1e3 / a.steps, "higher_is_better": True, "scaling": "weak",
+          "vs_baseline": None, "impl": "oracle_cpu", "dtype": "fp32", "data": "synthetic MNIST-shaped, random-init weights",
+          "timing": "host wall clock (perf_counter), one process, %d torch threads" % torch.get_num_threads(),
+          "config": {"model": "mnist_cnn_14var" + ("" if a.width_mult == 1 else "_x%d" % a.width_mult),
+                     "global_batch": B, "optimizer": "adam (TF1 formula)", "parallelism": "single process, CPU"},
+          "first_loss": first, "final_loss": float(loss)})
+    return 0
+
+
 def main() -> int:
     a = parse()
     # stdout carries exactly ONE line (the JSON): libraries that print banners there (NCCL's version line,
@@ -219,6 +256,8 @@ def main() -> int:
     if a.impl == "host_ps":
         from baseline.host_ps.bench_host_ps import run as run_host
         return run_host(a, emit)
+    if a.impl == "oracle_cpu":
+        return run_oracle_cpu(a, emit)
     if a.impl == "torch_graph":
         if int(os.environ.get("WORLD_SIZE", "1")) != a.gpus and a.gpus > 1:
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(a.gpus),
