@@ -83,6 +83,11 @@ class Config:
                                     # instead of one step per push (the reference's semantics, mnist_async/parameter_server.py:55-69)
     resident_owner: bool = True     # async + fused, dedicated PS GPU: serve pushes from ONE resident kernel instead of host-launched applies
     overlap_push: bool = True       # sync + fused: push/update/pull conv3..fc3 (98% of the bytes) while conv2/conv1 backward runs
+    debug_checksum: bool = False    # integrity checks: host transport - every push / pull message group carries an exact
+                                    # checksum that the receiver verifies; SPMD trainers - replicas compared bitwise after every
+                                    # sync step, reduced gradients checked against the workers' sums, async pushes accounted for
+    fault_inject: str = ""          # "" | corrupt_push:<step> | corrupt_pull:<step> | drop_rank:<step> - deliberate faults for the
+                                    # failure / race-detection tests (host transport; the first worker / first PS misbehaves)
     timeout_s: float = 120.0        # collective / rendezvous timeout (failure detection)
     log_time: bool = True           # print the reference's "Time:" line
 
@@ -105,7 +110,16 @@ class Config:
             raise ValueError("unsharded variants support exactly one parameter server (Q8)")
         if self.batch_size < 1:
             raise ValueError("batch_size must be positive")
+        if self.fault_inject:
+            kind, _, at = self.fault_inject.partition(":")
+            if kind not in ("corrupt_push", "corrupt_pull", "drop_rank") or not at.isdigit():
+                raise ValueError("fault_inject must be corrupt_push:<step>, corrupt_pull:<step> or drop_rank:<step>")
         return self
+
+    def fault_at(self, kind: str) -> int:
+        """step at which the fault `kind` fires, or -1"""
+        k, _, at = self.fault_inject.partition(":")
+        return int(at) if k == kind else -1
 
     def replace(self, **kw) -> "Config":
         return dataclasses.replace(self, **kw)
@@ -170,6 +184,11 @@ def build_parser(role: str = "worker") -> argparse.ArgumentParser:
                    help="async dedicated PS: host-launched apply kernels instead of the resident owner kernel")
     p.add_argument("--async-fold", dest="async_fold", action="store_true", default=_env_default("async_fold", False),
                    help="async + fused transport: fold all pushes pending at an apply into ONE optimizer step")
+    p.add_argument("--debug-checksum", dest="debug_checksum", action="store_true",
+                   default=_env_default("debug_checksum", False),
+                   help="verify every push / pull (host transport) and compare the replicas after every sync step (SPMD)")
+    p.add_argument("--fault-inject", dest="fault_inject", default=_env_default("fault_inject", ""),
+                   help="corrupt_push:<step> | corrupt_pull:<step> | drop_rank:<step> (tests of the integrity / failure checks)")
     p.add_argument("--timeout-s", type=float, default=_env_default("timeout_s", d.timeout_s))
     return p
 

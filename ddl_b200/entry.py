@@ -42,18 +42,28 @@ def run_role(role: str, variant: str, argv: Optional[Sequence[str]] = None):
             raise SystemExit("host transport needs world == P + W (got %d, P=%d, W=%d)"
                              % (world, cfg.num_ps, cfg.num_workers))
         host_ps.init_host_group(rank, world, cfg.timeout_s)
+        import torch.distributed as dist
         try:
             if role == "ps":
                 node = host_ps.HostPS(cfg, rank)
                 node.run()
-                return {"steps_served": node.steps_served}
-            node = host_ps.HostWorker(cfg, rank)
-            return {"final_accuracy": node.run()}
-        finally:
-            import torch.distributed as dist
+                out = {"steps_served": node.steps_served}
+            else:
+                node = host_ps.HostWorker(cfg, rank)
+                out = {"final_accuracy": node.run()}
+        except BaseException:
+            # a failed rank must die at once so that the launcher can stop the job: no farewell barrier,
+            # the peers would sit in it until the collective timeout
             if dist.is_initialized():
-                dist.barrier()
-                dist.destroy_process_group()
+                try:
+                    dist.destroy_process_group()
+                except Exception:                               # noqa: BLE001
+                    pass
+            raise
+        if dist.is_initialized():
+            dist.barrier()
+            dist.destroy_process_group()
+        return out
     from .parallel.trainer import SPMDTrainer
     kind = os.environ.get("DDL_LAYOUT", "auto")
     tr = SPMDTrainer(cfg, rank, world, local, kind)

@@ -13,6 +13,11 @@ Call-site mapping (reference -> here):
   pull ``Bcast(root=0)`` S/ps.py:69, S/worker.py:66                          -> ``dist.broadcast``
   pull ``Send``/``Recv`` SS/ps.py:126, SS/worker.py:94                       -> ``dist.send``/``recv``
 
+Debug mode (``--debug-checksum``): after the variables of one push (or pull) a [n, 2] int64 table of exact
+bit-pattern checksums follows on tag ``CK_TAG``; the receiver recomputes it from what arrived and raises on a mismatch.
+The reference's Q2 (a receive buffer overwritten while it is still being summed) is exactly the fault this catches;
+``--fault-inject corrupt_push:<step>`` / ``corrupt_pull:<step>`` plant one for the tests.
+
 Deviations, all deliberate: true gradient sum instead of the Q1/Q2 aliasing bugs
 (``quirk_parity`` reproduces them for study), plain tuples in the metadata (Q9), an initial pull
 so workers start from the PS weights (Q5), an async push that is received from ONE source end to
@@ -34,8 +39,12 @@ from ..models import make_spec, oracle
 from ..models.cnn import Model
 from ..optim import FlatOptimizer
 from ..utils import metrics as M
+from ..utils.verify import checksum_table, compare_tables
 from .arena import Arena
 from .sharding import make_plan
+
+
+CK_TAG = 900          # checksum tables travel on their own tag (variable tags are 0..14)
 
 
 def init_host_group(rank: int, world: int, timeout_s: float = 120.0) -> None:
@@ -91,13 +100,31 @@ class HostPS(_Common):
                 self.bucket[v].copy_(meta["resume_vars"][v])
 
     def _send_params(self, dst_workers: List[int]) -> None:
+        dbg = self.cfg.debug_checksum and bool(self.local_vars)
+        table = checksum_table([self.bucket[v] for v in self.local_vars]) if dbg else None
+        out = dict(self.bucket)
+        if self.rank == 0 and self.local_vars and self.cfg.fault_at("corrupt_pull") == self.steps_served and self.steps_served > 0:
+            v0 = self.local_vars[0]                             # planted fault: the message differs from the PS's copy
+            out[v0] = self.bucket[v0].clone()
+            out[v0].view(-1)[0] += 1.0
         if self.cfg.shard == "none" and self.cfg.mode == "sync":
             for v in self.local_vars:                           # Bcast over the world, S/ps.py:68-69
-                dist.broadcast(self.bucket[v], src=0)
+                dist.broadcast(out[v], src=0)
+            if dbg:
+                dist.broadcast(table, src=0)
         else:
             for w in dst_workers:                               # serial fan-out, SS/ps.py:124-126
                 for v in self.local_vars:
-                    dist.send(self.bucket[v], dst=w, tag=self.tag(v))
+                    dist.send(out[v], dst=w, tag=self.tag(v))
+                if dbg:
+                    dist.send(table, dst=w, tag=CK_TAG)
+
+    def _verify_push(self, tensors, src: int) -> None:
+        """debug mode: the checksum table that follows worker `src`'s variables must match what arrived"""
+        want = torch.zeros(len(self.local_vars), 2, dtype=torch.int64)
+        dist.recv(want, src=src, tag=CK_TAG)
+        compare_tables(checksum_table(tensors), want, ["v%d" % v for v in self.local_vars],
+                       "PS %d, push of rank %d, step %d" % (self.rank, src, self.steps_served))
 
     # -- loops ------------------------------------------------------------------------
     def _serve_sync(self) -> None:
@@ -109,6 +136,8 @@ class HostPS(_Common):
                 for w in workers:                               # rank order = the sync barrier
                     for v in self.local_vars:
                         dist.recv(recv[w][v], src=w, tag=self.tag(v))
+                    if self.cfg.debug_checksum:
+                        self._verify_push([recv[w][v] for v in self.local_vars], w)
                 for v in self.local_vars:
                     g = recv[workers[0]][v].clone()
                     if self.cfg.quirk_parity:                   # Q1: worker 0 counted twice
@@ -116,8 +145,8 @@ class HostPS(_Common):
                     for w in workers[1:]:
                         g += recv[w][v]
                     self.opt[v].step(self.bucket[v], g, gscale)
-                self._send_params(workers)
                 self.steps_served += 1
+                self._send_params(workers)
 
     def _serve_async(self) -> None:
         g = {v: torch.empty_like(self.bucket[v]) for v in self.local_vars}
@@ -127,11 +156,12 @@ class HostPS(_Common):
                 for v in self.local_vars:                       # one source per push (fixes Q4)
                     got = dist.recv(g[v], src=src, tag=self.tag(v))
                     src = got if src is None else src
+                if self.cfg.debug_checksum:
+                    self._verify_push([g[v] for v in self.local_vars], src)
                 for v in self.local_vars:
                     self.opt[v].step(self.bucket[v], g[v], 1.0)
-                for v in self.local_vars:                       # reply to that worker only, A/ps.py:68-69
-                    dist.send(self.bucket[v], dst=src, tag=self.tag(v))
                 self.steps_served += 1
+                self._send_params([src])                        # reply to that worker only, A/ps.py:68-69
 
     def run(self) -> None:
         self._handshake()
@@ -181,11 +211,43 @@ class HostWorker(_Common):
             for ps in range(self.P):
                 dist.send_object_list([meta], dst=ps)
 
-    def push(self) -> None:
+    def push(self, step: int = -1) -> None:
         grads = self.grads.views()
+        tables = None
+        if self.cfg.debug_checksum or self.cfg.fault_inject:
+            for v in self.order:
+                self.host_bucket[v].copy_(grads[v])
+            if self.cfg.debug_checksum:                         # what I MEANT to send, per owner
+                tables = {ps: checksum_table([self.host_bucket[v] for v in self.plan.shard_vars(ps)])
+                          for ps in range(self.P) if self.plan.shard_vars(ps)}
+            if self.windex == 0 and step >= 0 and self.cfg.fault_at("corrupt_push") == step:
+                self.host_bucket[self.order[0]].view(-1)[0] += 1.0      # planted fault: one element changes in flight
+            left = {ps: len(self.plan.shard_vars(ps)) for ps in range(self.P)}
+            for v in self.order:
+                ps = self.owner(v)
+                dist.send(self.host_bucket[v], dst=ps, tag=self.tag(v))
+                left[ps] -= 1
+                if tables is not None and left[ps] == 0:        # the table follows the PS's last variable directly, so
+                    dist.send(tables[ps], dst=ps, tag=CK_TAG)   # the message sequence per PS stays one contiguous group
+            return
         for v in self.order:                                    # 14 blocking sends, SS/worker.py:50-51
             self.host_bucket[v].copy_(grads[v])                 # device -> host (sess.run -> numpy)
             dist.send(self.host_bucket[v], dst=self.owner(v), tag=self.tag(v))
+
+    def _verify_pull(self, what: str) -> None:
+        """debug mode: one checksum table per PS follows its variables"""
+        bcast = self.cfg.shard == "none" and self.cfg.mode == "sync"
+        for ps in range(self.P):
+            vs = self.plan.shard_vars(ps)
+            if not vs:
+                continue
+            want = torch.zeros(len(vs), 2, dtype=torch.int64)
+            if bcast:
+                dist.broadcast(want, src=0)
+            else:
+                dist.recv(want, src=ps, tag=CK_TAG)
+            compare_tables(checksum_table([self.host_bucket[v] for v in vs]), want, ["v%d" % v for v in vs],
+                           "worker rank %d, %s from PS %d" % (self.rank, what, ps))
 
     def pull(self) -> None:
         for v in self.order:
@@ -193,6 +255,8 @@ class HostWorker(_Common):
                 dist.broadcast(self.host_bucket[v], src=0)      # S/worker.py:66
             else:
                 dist.recv(self.host_bucket[v], src=self.owner(v), tag=self.tag(v))   # SS/worker.py:94
+        if self.cfg.debug_checksum:
+            self._verify_pull("pull")
         views = self.params.views()
         with torch.no_grad():
             for v in self.order:                                # tf.assign, S/worker.py:69
@@ -206,6 +270,8 @@ class HostWorker(_Common):
             for ps in range(self.P):
                 for v in self.plan.shard_vars(ps):
                     dist.recv(self.host_bucket[v], src=ps, tag=self.tag(v))
+        if self.cfg.debug_checksum:
+            self._verify_pull("initial pull")
         self.params.load_vars(self.host_bucket)
 
     def run(self) -> float:
@@ -229,8 +295,12 @@ class HostWorker(_Common):
                     x = self.data.x_train[b:e].to(self.device, non_blocking=True)
                     y = self.data.y_train[b:e].to(self.device, non_blocking=True)
                     loss = self.model.compute_grads(x, y, step * self.W + self.windex)
+                if self.windex == 0 and cfg.fault_at("drop_rank") == step:
+                    import os
+                    print("[ddl] fault injection: rank %d exits at step %d" % (self.rank, step), flush=True)
+                    os._exit(17)
                 with self.timers.phase("push"):
-                    self.push()
+                    self.push(step)
                 with self.timers.phase("pull"):
                     self.pull()
                 self.losses.append(float(loss))

@@ -270,6 +270,9 @@ class SPMDTrainer:
         for epoch in range(cfg.epochs if not serve_only else 0):
             for cnt in range(nb):
                 loss = self.train_step(cnt)
+                if cfg.debug_checksum and cfg.mode == "sync":
+                    from ..utils.verify import replica_check
+                    replica_check(self, self.global_step)      # collective: every rank takes part
                 if lay.is_worker:
                     if cfg.eval_every and cnt % cfg.eval_every == 0:
                         with self.timers.phase("eval"):
@@ -282,6 +285,9 @@ class SPMDTrainer:
             self.transport.finish()
         if self.device.type == "cuda":
             torch.cuda.synchronize()
+        if cfg.debug_checksum and cfg.mode == "async":
+            from ..utils.verify import async_accounting
+            async_accounting(self)
         wall = time.perf_counter() - start_wall
         if lay.is_worker:
             acc = self.evaluate()

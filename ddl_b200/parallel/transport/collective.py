@@ -109,20 +109,54 @@ class CollectiveTransport(SpmdTransport):
     def barrier(self) -> None:
         dist.barrier()
 
+    def _grad_sums(self) -> torch.Tensor:
+        """debug mode: [P, 2] float64 - (sum, L1) of my gradient arena per shard, summed over all ranks"""
+        t = torch.stack([torch.stack([self.grads.shard(r).double().sum(), self.grads.shard(r).double().abs().sum()])
+                         for r in range(self.layout.num_ps)])
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return t
+
+    def _check_reduced(self, want: torch.Tensor) -> None:
+        """debug mode: what an owner holds after the reduction must be the sum of what the workers pushed -
+        a dropped, doubled or stale contribution (the reference's Q1 / Q2) moves the sum by a whole gradient, rounding
+        moves it by ~1e-7 of the L1 norm"""
+        for r in self.layout.my_shards:
+            got = float(self.grads.shard(r).double().sum())
+            tol = 1e-5 * float(want[r, 1]) + 1e-12
+            if abs(got - float(want[r, 0])) > tol:
+                from ...utils.verify import ChecksumError
+                raise ChecksumError("step %d, shard %d on rank %d: reduced gradient sums to %.9g, the workers pushed %.9g "
+                                    "(tolerance %.3g)" % (self.step_count, r, self.layout.rank, got, float(want[r, 0]), tol))
+
     def _sync_step(self) -> None:
         lay = self.layout
+        want = self._grad_sums() if self.cfg.debug_checksum else None
+        if lay.my_worker == 0 and self.cfg.fault_at("corrupt_push") == self.step_count:
+            self.grads.views()[0].view(-1)[0] += 1.0            # planted fault: a contribution changes after it was summed up
         if self.symmetric:
             mine = self.grads.shard(lay.rank)
             dist.reduce_scatter_tensor(mine, self.grads.flat, op=dist.ReduceOp.SUM)
+            if want is not None:
+                self._check_reduced(want)
             self.opts[lay.rank].step(self.params.shard(lay.rank), mine, self.gscale)
             dist.all_gather_into_tensor(self.params.flat, self.params.shard(lay.rank))
+            self._plant_pull_fault()
             return
         for r in range(lay.num_ps):
             dist.reduce(self.grads.shard(r), dst=lay.owner_rank(r), op=dist.ReduceOp.SUM)
+        if want is not None:
+            self._check_reduced(want)
         for r in lay.my_shards:
             self.opts[r].step(self.params.shard(r), self.grads.shard(r), self.gscale)
         for r in range(lay.num_ps):
             dist.broadcast(self.params.shard(r), src=lay.owner_rank(r))
+        self._plant_pull_fault()
+
+    def _plant_pull_fault(self) -> None:
+        lay = self.layout
+        if lay.my_worker == 0 and lay.num_workers > 1 and self.cfg.fault_at("corrupt_pull") == self.step_count:
+            v = next(v for v in range(len(self.plan.owner)) if lay.owner_rank(self.plan.owner[v]) != lay.rank)
+            self.params.views()[v].view(-1)[0] += 1.0           # planted fault: this replica installs a different value
 
     def _async_round(self) -> None:
         lay = self.layout

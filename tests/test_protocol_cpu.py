@@ -7,6 +7,7 @@ async = every push applied exactly once.
 import os
 import re
 import subprocess
+import time
 import sys
 
 import pytest
@@ -72,7 +73,9 @@ def test_config1_mnist_sync_1ps_2workers_log_format(tmp_path):
     ("mnist_sync_sharding_greedy", "nccl"),
 ])
 def test_sync_sharded_matches_oracle(tmp_path, variant, transport):
-    run_variant(variant, 2, 2, ["--max-steps", "3", "--transport", transport,
+    # --debug-checksum: every push / pull message group is verified (host), replicas and reduced gradients are compared
+    # after every step (collective); a clean run must pass all of it and still match the oracle
+    run_variant(variant, 2, 2, ["--max-steps", "3", "--transport", transport, "--debug-checksum",
                                 "--ckpt-path", str(tmp_path / "c.pt")])
     got, _ = load_vars(tmp_path / "c.pt")
     want = oracle_sync_run(2, 3)
@@ -93,7 +96,7 @@ def test_collective_flat_mean_and_adam_state(tmp_path):
 @pytest.mark.parametrize("variant,P,transport", [("mnist_async", 1, "host"), ("mnist_async_sharding", 2, "host"),
                                                  ("mnist_async_sharding_greedy", 2, "nccl")])
 def test_async_every_push_applied_once(tmp_path, variant, P, transport):
-    extra = ["--max-steps", "3", "--transport", transport]
+    extra = ["--max-steps", "3", "--transport", transport, "--debug-checksum"]     # incl. the push accounting at the end
     if transport == "nccl":
         extra += ["--ckpt-path", str(tmp_path / "c.pt")]
     out = run_variant(variant, P, 2, extra)
@@ -101,6 +104,26 @@ def test_async_every_push_applied_once(tmp_path, variant, P, transport):
     if transport == "nccl":
         _, blob = load_vars(tmp_path / "c.pt")
         assert blob["t"] == 3 * 2          # one optimizer step per push, W pushes per round
+
+
+@pytest.mark.parametrize("transport,fault,message", [
+    ("host", "corrupt_push:1", r"PS 0, push of rank 2, step 1: checksum mismatch for v\d+"),
+    ("host", "corrupt_pull:2", r"worker rank 2, pull from PS 0: checksum mismatch for v\d+"),
+    ("nccl", "corrupt_push:1", r"reduced gradient sums to .* the workers pushed"),
+    ("nccl", "corrupt_pull:1", r"worker ranks 2 and 3 hold different parameters for v\d+"),
+])
+def test_debug_checksum_catches_planted_faults(transport, fault, message):
+    """one element changed in flight (the effect of the reference's Q2 buffer reuse) is caught by the
+    receiver's checksum (host), by the reduced-gradient check or by the replica comparison (collective) - and the job
+    dies within seconds, not at the collective timeout."""
+    env = dict(os.environ, OMP_NUM_THREADS="2", DDL_LAUNCH_TIMEOUT="200", DDL_LAUNCH_ATTEMPTS="1")
+    cmd = ["bash", os.path.join(ROOT, "mnist_sync_sharding", "run.sh"), "2", "2"] + COMMON + \
+        ["--max-steps", "3", "--transport", transport, "--debug-checksum", "--fault-inject", fault]
+    t0 = time.time()
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=260, env=env)
+    assert r.returncode != 0, "the planted fault went unnoticed:\n" + r.stdout[-1500:]
+    assert re.search(message, r.stdout + r.stderr), (r.stdout + r.stderr)[-3000:]
+    assert time.time() - t0 < 100, "failure detection took %.0f s" % (time.time() - t0)
 
 
 def test_unsharded_rejects_two_ps():

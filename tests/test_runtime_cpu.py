@@ -121,3 +121,48 @@ def test_compat_model_surface():
     m.train_step(m.x_train[:20], m.y_train[:20])
     assert not torch.equal(before, m.var_bucket[12])
     assert 0.0 <= m.accuracy(m.x_test, m.y_test) <= 1.0
+
+
+def test_bit_checksums_are_exact_and_position_sensitive():
+    """utils/verify.py: the debug-mode checksum is over bit patterns - equal for equal data whatever the device order of
+    summation, different for one flipped bit, for two swapped elements and for -0.0 vs 0.0"""
+    from ddl_b200.utils.verify import bits_checksum, checksum_table, compare_tables, ChecksumError
+    g = torch.Generator().manual_seed(5)
+    a = torch.randn(1000, generator=g)
+    assert torch.equal(bits_checksum(a), bits_checksum(a.clone().view(10, 100)))
+    b = a.clone(); b[17] = torch.nextafter(b[17], torch.tensor(10.0))
+    assert not torch.equal(bits_checksum(a), bits_checksum(b))                       # one ulp
+    c = a.clone(); c[[3, 4]] = c[[4, 3]]
+    assert bits_checksum(a)[0] == bits_checksum(c)[0] and bits_checksum(a)[1] != bits_checksum(c)[1]   # a swap
+    z = torch.zeros(4); nz = z.clone(); nz[1] = -0.0
+    assert not torch.equal(bits_checksum(z), bits_checksum(nz))
+    t = checksum_table([a, z])
+    assert t.shape == (2, 2) and t.dtype == torch.int64
+    compare_tables(t, t.clone(), ["a", "z"], "self")
+    with pytest.raises(ChecksumError, match="checksum mismatch for z"):
+        compare_tables(checksum_table([a, nz]), t, ["a", "z"], "planted")
+    with pytest.raises(ChecksumError, match="entries"):
+        compare_tables(t[:1], t, ["a", "z"], "short")
+
+
+def test_fault_inject_flag_is_validated():
+    from ddl_b200.config import Config
+    c = Config(fault_inject="drop_rank:4").validate()
+    assert c.fault_at("drop_rank") == 4 and c.fault_at("corrupt_push") == -1 and Config().validate().fault_at("drop_rank") == -1
+    for bad in ("drop_rank", "explode:1", "corrupt_push:x"):
+        with pytest.raises(ValueError):
+            Config(fault_inject=bad).validate()
+
+
+def test_worker_dying_mid_run_stops_the_job(tmp_path):
+    """SURVEY 5.3 (the reference hangs forever when a rank dies): --fault-inject drop_rank:<step> kills the first worker
+    between two steps of a real run; the launcher reports its exit code and stops the PS and the other worker."""
+    env = dict(os.environ, OMP_NUM_THREADS="2", DDL_LAUNCH_TIMEOUT="200", DDL_LAUNCH_ATTEMPTS="1")
+    t0 = time.time()
+    r = subprocess.run(["bash", os.path.join(ROOT, "mnist_sync", "run.sh"), "1", "2"] + COMMON +
+                       ["--max-steps", "4", "--fault-inject", "drop_rank:2", "--timeout-s", "60"],
+                       capture_output=True, text=True, timeout=260, env=env)
+    assert r.returncode == 17, (r.returncode, (r.stdout + r.stderr)[-2000:])
+    assert "fault injection: rank 1 exits at step 2" in r.stdout
+    assert "stopping the job" in r.stderr
+    assert time.time() - t0 < 90
