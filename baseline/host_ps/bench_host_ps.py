@@ -25,8 +25,10 @@ def run(a, emit=lambda o: print(json.dumps(o))) -> int:
     steps = a.steps + max(3, a.warmup)
     with tempfile.TemporaryDirectory() as td:
         mpath = os.path.join(td, "m.jsonl")
-        extra = ["--synthetic", "--synthetic-train", str(max(6000, 100 * n * (steps + 1))), "--synthetic-test", "1000",
-                 "--seed", "1234", "--eval-every", "0", "--max-steps", str(steps), "--backend", "torch",
+        ev = int(getattr(a, "eval_every", 0) or 0)          # the reference evaluates every 10 batches INSIDE its timed region
+        rows = int(getattr(a, "test_rows", 10000)) if ev else 1000     # (mnist_sync/worker.py:71-72): bench.py --eval-every 10
+        extra = ["--synthetic", "--synthetic-train", str(max(6000, 100 * n * (steps + 1))), "--synthetic-test", str(rows),
+                 "--seed", "1234", "--eval-every", str(ev), "--max-steps", str(steps), "--backend", "torch",
                  "--metrics-path", mpath, "--batch-size", str(a.batch_size), "--width-mult", str(a.width_mult)]
         env_keep = {k: os.environ.pop(k) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_PORT") if k in os.environ}
         try:
@@ -39,6 +41,8 @@ def run(a, emit=lambda o: print(json.dumps(o))) -> int:
         rows = []
         for f in glob.glob(mpath + "*"):
             rows += [json.loads(l) for l in open(f) if "steady_samples_per_s" in l]
+    import torch
+    wdev = "gpu" if torch.cuda.is_available() else "cpu"
     slow = max(r["steady_s"] for r in rows)
     steady_steps = rows[0]["steady_steps"]
     emit({
@@ -47,5 +51,6 @@ def run(a, emit=lambda o: print(json.dumps(o))) -> int:
         "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (torch ops, TF32 off)", "impl": "host_ps",
         "data": "synthetic MNIST-shaped", "timing": "host wall clock, max over workers (transport is host-side)",
         "config": {"model": "mnist_cnn_14var", "variant": a.variant, "global_batch": a.batch_size * n,
-                   "parallelism": "ps%d(cpu)+w%d(gpu), host/gloo transport" % (n, n)}})
+                   "eval_every": int(getattr(a, "eval_every", 0) or 0),
+                   "parallelism": "ps%d(cpu)+w%d(%s), host/gloo transport" % (n, n, wdev)}})
     return 0
