@@ -251,7 +251,8 @@ def main() -> int:
         os.write(real_stdout, (json.dumps(obj) + "\n").encode())
 
     if a.impl == "reference":
-        emit({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE})
+        if int(os.environ.get("RANK", "0")) == 0:          # under torchrun every rank gets here: one line, from rank 0
+            emit({"impl": "reference", "unavailable": REFERENCE_UNAVAILABLE})
         return 0
     if a.impl == "host_ps":
         from baseline.host_ps.bench_host_ps import run as run_host
