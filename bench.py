@@ -258,7 +258,7 @@ def main() -> int:
         from baseline.host_ps.bench_host_ps import run as run_host
         return run_host(a, emit)
     if a.impl == "oracle_cpu":
-        return run_oracle_cpu(a, emit)
+        return run_oracle_cpu(a, emit) if int(os.environ.get("RANK", "0")) == 0 else 0
     if a.impl == "torch_graph":
         if int(os.environ.get("WORLD_SIZE", "1")) != a.gpus and a.gpus > 1:
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(a.gpus),
