@@ -313,13 +313,16 @@ def main():
         case_sync(rank, world, "colocated", "greedy", graphs=True, opt="adam", k4=False, nvls="off")
         case_sync_vs_nccl(rank, world, "colocated", "block", "adam", nvls="off")
     elif case == "sync_nvls_on":
+        # --nvls on raises when no multicast object can be bound (fused.py::_alloc_arena).  On an NVSwitch box (every B200
+        # box this suite targets) that is a FAILURE of this case, not a skip: the 4- and 8-GPU bench path depends on it.
+        # A machine without NVSwitch can opt out explicitly.
         try:
             case_sync(rank, world, "colocated", "greedy", graphs=True, opt="adam", k4=False, nvls="on")
             case_sync_vs_nccl(rank, world, "colocated", "block", "adam", nvls="on")
         except Exception as e:                       # noqa: BLE001
-            if "NVLS multicast" not in str(e):
+            if "NVLS multicast" not in str(e) or os.environ.get("DDL_TEST_ALLOW_NO_NVLS", "0") != "1":
                 raise
-            print("no NVLS on this box: %s" % e, flush=True)
+            print("no NVLS on this box (DDL_TEST_ALLOW_NO_NVLS=1): %s" % e, flush=True)
     elif case == "async_sgd":
         case_async_counting(rank, world, "sgd")
     elif case == "async_adam":
