@@ -97,3 +97,32 @@ def test_committed_sass_evidence_belongs_to_the_sources_in_the_tree():
     for name in ("tc_act_gemm_kernel", "tc_wgrad_kernel", "tc_patch_conv_kernel"):
         listing = open(os.path.join(root, "profiles", "sass", name + ".txt")).read()
         assert "UTCHMMA" in listing and "UTMALDG" in listing and m.group(1) in listing
+
+
+def test_baseline_tables_quote_the_committed_bench_lines():
+    """BASELINE.md section 6 is regenerated from the JSON lines under profiles/r2_*: every line's samples/s value must
+    appear in the document (thousands separators), so a table row cannot outlive the measurement it came from."""
+    import glob
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "BASELINE.md")).read()
+    files = sorted(glob.glob(os.path.join(root, "profiles", "r2_8gpu", "*.json")) +
+                   glob.glob(os.path.join(root, "profiles", "r2_scale", "*.json")))
+    assert len(files) >= 15
+    seen = 0
+    for f in files:
+        for line in open(f):
+            line = line.strip()
+            if not (line.startswith("{") and '"metric"' in line):
+                continue
+            d = json.loads(line)
+            if os.path.basename(f) == "async_dedicated_1ps_1w_n2.json":
+                continue                                  # 2-GPU plumbing check of the dedicated layout, not a table row
+            v = "{:,}".format(int(round(d["value"])))
+            assert v in text, "%s: %s samples/s is not quoted in BASELINE.md" % (os.path.relpath(f, root), v)
+            if isinstance(d.get("e2e"), dict) and d.get("impl", "ours") == "ours" and "r2_8gpu" in f:
+                e = "{:,}".format(int(round(d["e2e"]["value"])))
+                assert e in text, "%s: e2e %s is not quoted in BASELINE.md" % (os.path.relpath(f, root), e)
+            seen += 1
+    assert seen >= 15
