@@ -147,3 +147,31 @@ def test_single_and_resume(tmp_path):
     want = oracle_sync_run(1, 4)
     for g, w in zip(full, want):
         assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
+
+
+def test_mlp_variant_sync_sharded_matches_oracle(tmp_path):
+    """BASELINE config 5 names a widened CNN / MLP: the 6-variable MLP (784 - 1024 - 512 - 10, same fc2-without-ReLU and
+    dropout placement as model.py:67-87) through the sharded sync PS path, against the sequential oracle."""
+    from ddl_b200.data import synthetic_mnist
+    from ddl_b200.models import oracle
+    from ddl_b200.models.spec import make_spec
+    run_variant("mnist_sync_sharding_greedy", 2, 2, ["--model", "mlp", "--max-steps", "3", "--transport", "nccl",
+                                                     "--debug-checksum", "--ckpt-path", str(tmp_path / "m.pt")])
+    blob = torch.load(tmp_path / "m.pt", map_location="cpu", weights_only=False)
+    assert sorted(blob["vars"]) == ["mnist/v%d" % i for i in range(6)] and blob["t"] == 3
+    assert tuple(blob["vars"]["mnist/v0"].shape) == (784, 1024) and tuple(blob["vars"]["mnist/v4"].shape) == (512, 10)
+    spec = make_spec("mlp", 1)
+    d = synthetic_mnist(240, 60, 3)
+    p = oracle.init_params(spec, 3)
+    opts = [oracle.OracleOptimizer(q, "adam", 1e-3) for q in p]
+    for s in range(3):
+        gsum = [torch.zeros_like(q) for q in p]
+        for w in range(2):
+            b, e = d.batch_slice(s, 20, w, 2, False)
+            _, g, _ = oracle.loss_and_grads(p, d.x_train[b:e], d.y_train[b:e], spec, 0.5, None, 3, s * 2 + w)
+            for a, gi in zip(gsum, g):
+                a += gi
+        for q, o, g in zip(p, opts, gsum):
+            o.step(q, g)
+    for i, w in enumerate(p):
+        assert torch.allclose(blob["vars"]["mnist/v%d" % i], w, atol=2e-5, rtol=1e-4), i
