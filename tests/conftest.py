@@ -9,6 +9,13 @@ if ROOT not in sys.path:
 
 
 def pytest_configure(config):
+    # In-process oracle math: on the small virtualised CPUs these suites run on, torch's default (one thread per vCPU)
+    # is 10x SLOWER than two threads (bench.py --impl oracle_cpu: 27 vs 430 samples/s) - oversubscribed OpenMP spinning.
+    try:
+        import torch
+        torch.set_num_threads(int(os.environ.get("DDL_TEST_THREADS", "2")))
+    except Exception:                                            # noqa: BLE001
+        pass
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on a B200)")
     config.addinivalue_line("markers", "multigpu: needs >= 2 CUDA devices")
 

@@ -175,3 +175,29 @@ def test_mlp_variant_sync_sharded_matches_oracle(tmp_path):
             o.step(q, g)
     for i, w in enumerate(p):
         assert torch.allclose(blob["vars"]["mnist/v%d" % i], w, atol=2e-5, rtol=1e-4), i
+
+
+def test_quirk_parity_replicated_data_and_sgd(tmp_path):
+    """The parity switches of SURVEY 2.5 in one run of the host rung: --quirk-parity reproduces Q1 (the PS sums worker
+    0's gradient twice, mnist_sync_sharding/parameter_server.py:78-80), --replicate-data reproduces Q6 (every worker
+    reads rows [bs*cnt, bs*(cnt+1)), mnist_sync/worker.py:27-28), --optimizer sgd is the third optimizer kind."""
+    from ddl_b200.data import synthetic_mnist
+    from ddl_b200.models import oracle
+    from ddl_b200.models.spec import REFERENCE_SPEC as spec
+    run_variant("mnist_sync_sharding", 2, 2, ["--max-steps", "3", "--transport", "host", "--quirk-parity", "--replicate-data",
+                                              "--optimizer", "sgd", "--debug-checksum", "--ckpt-path", str(tmp_path / "q.pt")])
+    got, _ = load_vars(tmp_path / "q.pt")
+    d = synthetic_mnist(240, 60, 3)
+    p = oracle.init_params(spec, 3)
+    plain = [q.clone() for q in p]
+    for s in range(3):
+        b, e = d.batch_slice(s, 20, 0, 2, True)                 # the same rows for both workers
+        gs = [oracle.loss_and_grads(p, d.x_train[b:e], d.y_train[b:e], spec, 0.5, None, 3, s * 2 + w)[1] for w in range(2)]
+        gp = [oracle.loss_and_grads(plain, d.x_train[b:e], d.y_train[b:e], spec, 0.5, None, 3, s * 2 + w)[1] for w in range(2)]
+        for q, g0, g1 in zip(p, gs[0], gs[1]):
+            q -= 1e-3 * (2 * g0 + g1)                           # Q1: worker 0 counted twice
+        for q, g0, g1 in zip(plain, gp[0], gp[1]):
+            q -= 1e-3 * (g0 + g1)
+    for g, w in zip(got, p):
+        assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
+    assert any(not torch.allclose(g, w, atol=2e-5, rtol=1e-4) for g, w in zip(got, plain)), "the quirk changed nothing"
