@@ -166,3 +166,38 @@ def test_worker_dying_mid_run_stops_the_job(tmp_path):
     assert "fault injection: rank 1 exits at step 2" in r.stdout
     assert "stopping the job" in r.stderr
     assert time.time() - t0 < 90
+
+
+def test_reference_mnist_pkl_is_read_from_the_variant_directory(tmp_path):
+    """mnist_sync/model/model.py:8-14: ``data/mnist.pkl`` = pickle of (train, valid, test), each (x[N,784] float32, y[N]
+    int64), read with encoding='latin1', relative to the directory the script runs in.  A user of the reference brings
+    that file; single.py must train on it (not on the synthetic fallback) and the compat Model must expose it with
+    one-hot labels like pd.get_dummies."""
+    import pickle
+    import shutil
+    import numpy as np
+    rng = np.random.RandomState(0)
+    tmpl = (rng.rand(10, 784) < 0.15).astype(np.float32)
+
+    def split(n):
+        y = rng.randint(0, 10, size=n).astype(np.int64)
+        return (tmpl[y] * 0.8 + 0.1 * rng.rand(n, 784)).astype(np.float32), y
+    vdir = tmp_path / "mnist_sync"
+    shutil.copytree(os.path.join(ROOT, "mnist_sync"), vdir)
+    os.makedirs(vdir / "data")
+    train, valid, test = split(200), split(20), split(50)
+    with open(vdir / "data" / "mnist.pkl", "wb") as f:
+        pickle.dump((train, valid, test), f, protocol=2)
+    from ddl_b200.data import load_dataset
+    d = load_dataset(str(vdir / "data" / "mnist.pkl"))
+    assert not d.synthetic and d.num_train == 200 and tuple(d.x_test.shape) == (50, 784)
+    assert d.y_train.dtype == torch.int32 and torch.equal(d.y_train.long(), torch.from_numpy(train[1]))
+    oh = d.one_hot_train()
+    assert tuple(oh.shape) == (200, 10) and torch.equal(oh.argmax(1), torch.from_numpy(train[1]))
+    env = dict(os.environ, OMP_NUM_THREADS="2", PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, "single.py", "--device", "cpu", "--batch-size", "20", "--max-steps", "3",
+                        "--eval-every", "2", "--seed", "1", "--metrics-path", str(tmp_path / "m.jsonl")],
+                       cwd=str(vdir), capture_output=True, text=True, timeout=240, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "synthetic" not in r.stdout                          # the fallback prints a notice; the file was found
+    assert "final accuracy" in r.stdout
