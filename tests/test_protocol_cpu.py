@@ -201,3 +201,30 @@ def test_quirk_parity_replicated_data_and_sgd(tmp_path):
     for g, w in zip(got, p):
         assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
     assert any(not torch.allclose(g, w, atol=2e-5, rtol=1e-4) for g, w in zip(got, plain)), "the quirk changed nothing"
+
+
+def test_widened_model_single_matches_oracle(tmp_path):
+    """BASELINE config 5 (the widened model, here x2 so that a CPU can carry it): channel counts and FC widths scale, the
+    10-class head does not; single.py against the oracle built from the same spec."""
+    from ddl_b200.data import synthetic_mnist
+    from ddl_b200.models import oracle
+    from ddl_b200.models.spec import make_spec
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    ck = str(tmp_path / "w.pt")
+    r = subprocess.run([sys.executable, "single.py"] + COMMON + ["--width-mult", "2", "--max-steps", "2", "--ckpt-path", ck],
+                       cwd=os.path.join(ROOT, "mnist_sync"), capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    got, blob = load_vars(ck)
+    spec = make_spec("cnn", 2)
+    assert spec.num_params == sum(g.numel() for g in got) and tuple(got[6].shape) == (5, 5, 256, 512)
+    assert tuple(got[8].shape) == (2048, 2048) and tuple(got[12].shape) == (1024, 10)
+    d = synthetic_mnist(240, 60, 3)
+    p = oracle.init_params(spec, 3)
+    opts = [oracle.OracleOptimizer(q, "adam", 1e-3) for q in p]
+    for s in range(2):
+        b, e = d.batch_slice(s, 20, 0, 1, False)
+        _, g, _ = oracle.loss_and_grads(p, d.x_train[b:e], d.y_train[b:e], spec, 0.5, None, 3, s)
+        for q, o, gi in zip(p, opts, g):
+            o.step(q, gi)
+    for g, w in zip(got, p):
+        assert torch.allclose(g, w, atol=2e-5, rtol=1e-4)
