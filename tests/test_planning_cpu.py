@@ -97,6 +97,17 @@ def test_committed_sass_evidence_belongs_to_the_sources_in_the_tree():
     for name in ("tc_act_gemm_kernel", "tc_wgrad_kernel", "tc_patch_conv_kernel"):
         listing = open(os.path.join(root, "profiles", "sass", name + ".txt")).read()
         assert "UTCHMMA" in listing and "UTMALDG" in listing and m.group(1) in listing
+    # the whole-library counts of the table are what cuobjdump says about the shipped .so right now
+    import shutil, subprocess
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if os.path.exists(exe) and not build.needs_build():
+        sass = subprocess.run([exe, "-sass", build.LIB], capture_output=True, text=True).stdout
+        row = re.search(r"\| \*\*whole library\*\* \| \| (\d+) \| (\d+) \| (\d+) \| (\d+) \|", text)
+        assert row, "no whole-library row in profiles/sass_evidence.md"
+        lines = sass.splitlines()
+        count = lambda k: sum(1 for ln in lines if re.search(r"(?<![A-Z])" + k, ln))
+        assert [int(x) for x in row.groups()] == [count("UTCHMMA"), count("UTMALDG"), count("UTMASTG"), count("LDTM")]
+        assert count("HMMA") == 0                            # no legacy mma.sync anywhere
 
 
 def test_baseline_tables_quote_the_committed_bench_lines():
