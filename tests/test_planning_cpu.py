@@ -84,6 +84,25 @@ def test_fc3_fused_kernel_shape_limits():
     assert L.ddl_fc3_fused_fits(100, 510, 10) == 0      # K % 4
 
 
+def test_patch_resident_conv_selection_rule():
+    """csrc/tc_patch.cu host side: the patch kernel needs the padded patch [H+4][W+4][cin] plus a weight ring in 227 KB of
+    shared memory and channel counts in multiples of 32; it is PREFERRED only where >= 70% of its M rows are real pixels
+    (pad columns are M rows): the reference model's conv2 (14x14) yes, conv3 (7x7: 38%) and conv4 (4x4) no
+    (profiles/patch_conv_r2.md)."""
+    L = _lib()
+    assert L.ddl_patch_conv_fits(14, 14, 32, 64) == 1 and L.ddl_patch_conv_preferred(14, 14, 32, 64) == 1     # conv2
+    assert L.ddl_patch_conv_fits(7, 7, 64, 128) == 1 and L.ddl_patch_conv_preferred(7, 7, 64, 128) == 0       # conv3
+    assert L.ddl_patch_conv_preferred(4, 4, 128, 256) == 0                                                    # conv4
+    assert L.ddl_patch_conv_fits(14, 14, 33, 64) == 0                          # channels not a multiple of 32
+    assert L.ddl_patch_conv_fits(14, 14, 192, 384) == 0                        # widened x6 conv2: the patch does not fit
+    assert L.ddl_patch_conv_preferred(14, 14, 64, 128) == 1                    # widened x2 conv2 still does
+    for H, cin, cout in [(14, 32, 64), (7, 64, 128), (28, 32, 32), (10, 32, 96)]:
+        if L.ddl_patch_conv_preferred(H, H, cin, cout):
+            rpt = 128 // (H + 4)
+            tiles = -(-H // rpt)
+            assert H * H / (tiles * 128.0) >= 0.7
+
+
 def test_committed_sass_evidence_belongs_to_the_sources_in_the_tree():
     """profiles/sass_evidence.md and profiles/sass/*.txt are generated from the built library (tools/sass_extract.py, also
     run by ``python -m ddl_b200.ops.build -v``); the digest they quote must be the digest of the sources as they are now."""
